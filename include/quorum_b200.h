@@ -1,0 +1,113 @@
+/* quorum_b200 — C ABI of the B200 (sm_100a) thinking-tag filter + concatenate path.
+ *
+ * The reference (andrewginns/quorum) has no FFI: the hot path is reached through two module-level Python
+ * names and two inline `str.join` expressions in src/quorum/oai_proxy.py.  This header is what a binding for
+ * that path binds instead; every entry point cites the reference code it replaces.  All pointers are plain
+ * pointers + sizes (no torch types).  Unless stated otherwise every data pointer is a DEVICE pointer, all
+ * offsets are int64 byte offsets into the flat buffer they index, and the call is asynchronous on `stream`
+ * (a cudaStream_t passed as void*).  The library allocates no device memory: scratch is caller-owned, its size
+ * comes from the *_scratch_bytes query.
+ *
+ * Return value: 0 on success, a negative QB200_E* code otherwise; qb200_last_error() gives the message of the
+ * last failing call on the calling thread.  There is no CPU fallback: without a CUDA device every compute
+ * entry point fails with QB200_ECUDA.
+ *
+ * Text must be (generalised) UTF-8: the automata look only at ASCII bytes and the multi-byte forms listed in
+ * DESIGN.md; every other byte passes through untouched.
+ */
+#ifndef QUORUM_B200_H
+#define QUORUM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QB200_OK 0
+#define QB200_EINVAL (-1)   /* bad argument (NULL, negative count, misaligned base, capacity too small) */
+#define QB200_ETAGS (-2)    /* unsupported tag table (see qb200_tags_create) */
+#define QB200_ECUDA (-3)    /* CUDA runtime error (no device, launch failure) */
+#define QB200_ESCRATCH (-4) /* scratch buffer too small */
+
+#define QB200_MAX_TAGS 16    /* distinct (case-folded) names */
+#define QB200_MAX_TAG_LEN 22 /* bytes per name */
+#define QB200_HELD_MAX 23    /* longest partial tag a stream can carry, in bytes */
+
+/* flags */
+#define QB200_HIDE 1u        /* strip_concat: apply the filter + .strip()  (hide_final_think, oai_proxy.py:134-139) */
+#define QB200_STREAM_JOIN 2u /* strip_concat: streaming-final join, drop inputs that are empty BEFORE the filter (oai_proxy.py:760-764) */
+#define QB200_FLUSH 4u       /* stream_feed: apply ThinkingTagFilter.flush() after the last chunk (oai_proxy.py:739, 352-371) */
+
+typedef struct qb200_tags qb200_tags; /* opaque, host-side */
+
+/* Per-stream carried state of ThinkingTagFilter (oai_proxy.py:275-276: self.buffer, self.thinking_depth).
+ * `held` is the part of the reference's buffer that can still matter: at depth 0 a holdable partial open tag
+ * (oai_proxy.py:311-323), at depth>0 a partial open/close tag at the very end (oai_proxy.py:332-334).
+ * `tail_len` lets a host mirror `self.buffer` exactly: number of bytes fed by this call after the last tag it
+ * consumed, or -1 when it consumed none. */
+typedef struct {
+    int32_t depth;
+    int32_t tail_len;
+    uint8_t held_len;
+    uint8_t held[QB200_HELD_MAX];
+} qb200_stream_state; /* 32 bytes */
+
+/* Thread-local message of the last failing call. */
+const char *qb200_last_error(void);
+
+/* Build the tag table.  Replaces the pattern construction of strip_thinking_tags (oai_proxy.py:137-138) and
+ * ThinkingTagFilter.__init__ (oai_proxy.py:270-276): names are case-folded and de-duplicated; an empty list means
+ * the pattern "<()>" with hold-back disabled, exactly as the reference behaves.
+ * `names` (HOST pointer): concatenated name bytes; `name_off` (HOST, n_tags+1 entries).
+ * Supported names: printable ASCII without regex metacharacters and without '<' '>' '/', at most QB200_MAX_TAG_LEN
+ * bytes, at most QB200_MAX_TAGS distinct names, at most 128 backreference classes in total (2^(number of 'i' and
+ * 's' letters) per name).  Anything else is rejected with QB200_ETAGS rather than approximated. */
+int qb200_tags_create(const uint8_t *names, const int32_t *name_off, int32_t n_tags, qb200_tags **out);
+void qb200_tags_destroy(qb200_tags *tags);
+
+/* strip_thinking_tags over n_resp responses fused with the concatenate join over n_req requests.
+ *   replaces  strip_thinking_tags                       oai_proxy.py:120-139
+ *             non-stream concatenate                    oai_proxy.py:1194-1199 + 1286 (1279, 1284)
+ *             streaming-final concatenate               oai_proxy.py:759-764 + 841 (834, 839)   [QB200_STREAM_JOIN;
+ *                                                       the caller passes "\n"+separator as `sep`]
+ * Response r is in_bytes[in_off[r] .. in_off[r+1]).  Request q joins responses req_off[q] .. req_off[q+1]-1 in
+ * order with `sep` between consecutive INCLUDED responses (all of them, or with QB200_STREAM_JOIN those whose
+ * input length is > 0).  req_off == NULL means one response per request (n_req must equal n_resp): plain batched
+ * strip_thinking_tags.  Without QB200_HIDE the bytes are copied unchanged (hide flag False, oai_proxy.py:134-135).
+ * Outputs: request q's text is out_bytes[out_off[q] .. out_off[q+1]) (out_off has n_req+1 entries, out_off[0]=0);
+ * resp_out_len (optional, n_resp entries) receives each response's filtered length (0 for excluded ones).
+ * out_capacity must be >= in_off[n_resp] + sep_len * n_resp.   in_bytes and out_bytes must be 16-byte aligned. */
+size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req);
+int qb200_strip_concat_batch(const qb200_tags *tags, const uint8_t *in_bytes, const int64_t *in_off, int64_t n_resp,
+                             const int64_t *req_off, int64_t n_req, const uint8_t *sep, int32_t sep_len,
+                             uint32_t flags, uint8_t *out_bytes, int64_t out_capacity, int64_t *out_off,
+                             int64_t *resp_out_len, void *scratch, size_t scratch_bytes, void *stream);
+
+/* ThinkingTagFilter.feed over many streams x many chunks, state carried in and out.
+ *   replaces  ThinkingTagFilter.feed                    oai_proxy.py:278-350
+ *             ThinkingTagFilter.flush                   oai_proxy.py:352-371   [QB200_FLUSH]
+ *             the per-backend filter objects            oai_proxy.py:543-545, 618-624, 739-741
+ * Chunk c is chunk_bytes[chunk_off[c] .. chunk_off[c+1]); stream s owns chunks stream_off[s] .. stream_off[s+1]-1,
+ * fed in order (stream_off[0] = 0, stream_off[n_streams] = n_chunks; a stream's chunks are contiguous).
+ * state_in == NULL starts every stream fresh (depth 0, nothing held); state_out may alias state_in or be NULL.
+ * Outputs: the return value of the feed of chunk c is out_bytes[out_chunk_off[c] .. out_chunk_off[c+1])
+ * (n_chunks+1 entries).  out_capacity must be >= chunk_off[n_chunks] + QB200_HELD_MAX * n_streams. */
+size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams);
+int qb200_stream_feed_batch(const qb200_tags *tags, const uint8_t *chunk_bytes, const int64_t *chunk_off,
+                            int64_t n_chunks, const int64_t *stream_off, int64_t n_streams,
+                            const qb200_stream_state *state_in, qb200_stream_state *state_out, uint32_t flags,
+                            uint8_t *out_bytes, int64_t out_capacity, int64_t *out_chunk_off, void *scratch,
+                            size_t scratch_bytes, void *stream);
+
+/* ThinkingTagFilter.flush for n streams without feeding (oai_proxy.py:352-371): drops the held partial, keeps depth. */
+int qb200_stream_flush_batch(qb200_stream_state *state, int64_t n_streams, void *stream);
+
+/* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
+int64_t qb200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

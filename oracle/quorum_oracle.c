@@ -11,7 +11,7 @@
  * The arithmetic lives in CPython's re/_sre and str (reference pins Python 3.13; fold tables
  * verified exhaustively on 3.12.3, see oracle/quorum_oracle.py header and tests/golden/fold_tables.json).
  * Parity pinning: tests/test_oracle_golden.py runs this library against the reference's own
- * exact-string test vectors and against tests/golden/*.json (outputs of the unmodified reference).
+ * exact-string test vectors and against tests/golden/ JSON fixtures (outputs of the unmodified reference).
  *
  * The batch entry points take the same buffers as the CUDA C-ABI (include/quorum_b200.h) but in host
  * memory, so the tests can compare output buffers byte for byte.

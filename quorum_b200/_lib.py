@@ -1,0 +1,69 @@
+"""ctypes binding of the C ABI declared in include/quorum_b200.h.  Fails loudly when the CUDA library is missing:
+there is no CPU path in this package."""
+from __future__ import annotations
+
+import ctypes
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libquorum_b200.so")
+
+QB200_HIDE, QB200_STREAM_JOIN, QB200_FLUSH = 1, 2, 4
+HELD_MAX = 23
+STATE_BYTES = 32
+
+EXPORTS = [
+    "qb200_last_error", "qb200_tags_create", "qb200_tags_destroy", "qb200_strip_concat_scratch_bytes",
+    "qb200_strip_concat_batch", "qb200_stream_feed_scratch_bytes", "qb200_stream_feed_batch",
+    "qb200_stream_flush_batch", "qb200_launch_count",
+]
+
+_lib = None
+
+
+class QuorumB200Error(RuntimeError):
+    pass
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(LIB_PATH):
+        raise QuorumB200Error(
+            f"{LIB_PATH} is missing: build it with `python -m quorum_b200.build` (nvcc, sm_100a). "
+            "quorum_b200 has no CPU fallback.")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, i64, i32, u32, sz = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32, ctypes.c_uint32, ctypes.c_size_t
+    L.qb200_last_error.restype = ctypes.c_char_p
+    L.qb200_last_error.argtypes = []
+    L.qb200_tags_create.restype = ctypes.c_int
+    L.qb200_tags_create.argtypes = [vp, vp, i32, ctypes.POINTER(vp)]
+    L.qb200_tags_destroy.restype = None
+    L.qb200_tags_destroy.argtypes = [vp]
+    L.qb200_strip_concat_scratch_bytes.restype = sz
+    L.qb200_strip_concat_scratch_bytes.argtypes = [i64, i64]
+    L.qb200_strip_concat_batch.restype = ctypes.c_int
+    L.qb200_strip_concat_batch.argtypes = [vp, vp, vp, i64, vp, i64, vp, i32, u32, vp, i64, vp, vp, vp, sz, vp]
+    L.qb200_stream_feed_scratch_bytes.restype = sz
+    L.qb200_stream_feed_scratch_bytes.argtypes = [i64, i64]
+    L.qb200_stream_feed_batch.restype = ctypes.c_int
+    L.qb200_stream_feed_batch.argtypes = [vp, vp, vp, i64, vp, i64, vp, vp, u32, vp, i64, vp, vp, sz, vp]
+    L.qb200_stream_flush_batch.restype = ctypes.c_int
+    L.qb200_stream_flush_batch.argtypes = [vp, i64, vp]
+    L.qb200_launch_count.restype = i64
+    L.qb200_launch_count.argtypes = []
+    _lib = L
+    return L
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = lib().qb200_last_error().decode("utf-8", "replace")
+        if rc == -2:
+            raise ValueError(f"quorum_b200: {msg}")
+        raise QuorumB200Error(f"quorum_b200 error {rc}: {msg}")
+
+
+def launch_count() -> int:
+    return int(lib().qb200_launch_count())

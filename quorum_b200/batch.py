@@ -1,0 +1,268 @@
+"""Batched device entry points: torch.uint8 / int64 CUDA tensors in, CUDA tensors out, through the C ABI.
+
+These are the calls a batching front end makes (one call per batch of responses or of stream chunks).  torch is
+used for device memory and the current stream only; all compute is in libquorum_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import QB200_FLUSH, QB200_HIDE, QB200_STREAM_JOIN, STATE_BYTES, check, lib
+
+
+class TagTable:
+    """Host-side handle of the tag table (qb200_tags_create).  Mirrors how the reference turns `thinking_tags` into its
+    patterns (oai_proxy.py:137-138, 270-274); unsupported names raise ValueError instead of being approximated."""
+
+    def __init__(self, tags: Sequence[str]):
+        tags = list(tags)
+        for t in tags:
+            if not isinstance(t, str):
+                raise TypeError("thinking_tags must be a list of str")
+        try:
+            bs = [t.encode("ascii") for t in tags]
+        except UnicodeEncodeError:
+            raise ValueError("quorum_b200: tag names must be ASCII")
+        off = (ctypes.c_int32 * (len(bs) + 1))()
+        for i, b in enumerate(bs):
+            off[i + 1] = off[i] + len(b)
+        names = ctypes.create_string_buffer(b"".join(bs) + b"\0")
+        h = ctypes.c_void_p()
+        check(lib().qb200_tags_create(ctypes.cast(names, ctypes.c_void_p), ctypes.cast(off, ctypes.c_void_p), len(bs),
+                                      ctypes.byref(h)))
+        self._h = h
+        self._destroy = lib().qb200_tags_destroy
+        self.tags = tags
+
+    @property
+    def handle(self) -> ctypes.c_void_p:
+        return self._h
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            try:
+                self._destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+
+_TABLES: dict = {}
+
+
+def tag_table(tags: Sequence[str]) -> TagTable:
+    key = tuple(tags)
+    t = _TABLES.get(key)
+    if t is None:
+        if len(_TABLES) > 256:
+            _TABLES.clear()
+        t = _TABLES[key] = TagTable(key)
+    return t
+
+
+def _require_cuda(t: torch.Tensor, dtype: torch.dtype, name: str) -> None:
+    if not t.is_cuda:
+        raise _lib.QuorumB200Error(f"{name} must be a CUDA tensor: quorum_b200 has no CPU path")
+    if t.dtype != dtype or not t.is_contiguous():
+        raise ValueError(f"{name} must be a contiguous {dtype} tensor")
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream_ptr(dev: torch.device):
+    return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def strip_concat_batch(tags: TagTable, in_bytes: torch.Tensor, in_off: torch.Tensor,
+                       req_off: Optional[torch.Tensor], sep: Optional[torch.Tensor], *, hide: bool, streaming: bool,
+                       out_bytes: Optional[torch.Tensor] = None, out_off: Optional[torch.Tensor] = None,
+                       resp_out_len: Optional[torch.Tensor] = None, scratch: Optional[torch.Tensor] = None,
+                       want_resp_len: bool = False):
+    """strip_thinking_tags over every response + the concatenate join per request (qb200_strip_concat_batch).
+
+    in_bytes: uint8[total]; in_off: int64[n_resp+1]; req_off: int64[n_req+1] or None (one response per request);
+    sep: uint8[sep_len] device tensor (for the streaming-final join pass "\\n"+separator, oai_proxy.py:841).
+    Returns (out_bytes, out_off, resp_out_len or None); request q is out_bytes[out_off[q]:out_off[q+1]].
+    Nothing is synchronised: results are ordered on the current stream.
+    """
+    dev = in_off.device
+    _require_cuda(in_off, torch.int64, "in_off")
+    _require_cuda(in_bytes, torch.uint8, "in_bytes")
+    n_resp = in_off.numel() - 1
+    if req_off is not None:
+        _require_cuda(req_off, torch.int64, "req_off")
+        n_req = req_off.numel() - 1
+    else:
+        n_req = n_resp
+    sep_len = 0 if sep is None else sep.numel()
+    if sep is not None:
+        _require_cuda(sep, torch.uint8, "sep")
+    with torch.cuda.device(dev):
+        if out_bytes is None:
+            out_bytes = torch.empty(in_bytes.numel() + sep_len * max(n_resp, 1) + 16, dtype=torch.uint8, device=dev)
+        if out_off is None:
+            out_off = torch.empty(n_req + 1, dtype=torch.int64, device=dev)
+        if resp_out_len is None and want_resp_len:
+            resp_out_len = torch.empty(max(n_resp, 1), dtype=torch.int64, device=dev)
+        need = lib().qb200_strip_concat_scratch_bytes(n_resp, n_req)
+        if scratch is None or scratch.numel() < need:
+            scratch = torch.empty(need, dtype=torch.uint8, device=dev)
+        flags = (QB200_HIDE if hide else 0) | (QB200_STREAM_JOIN if streaming else 0)
+        check(lib().qb200_strip_concat_batch(
+            tags.handle, _ptr(in_bytes), _ptr(in_off), n_resp, _ptr(req_off), n_req, _ptr(sep), sep_len, flags,
+            _ptr(out_bytes), out_bytes.numel(), _ptr(out_off), _ptr(resp_out_len), _ptr(scratch), scratch.numel(),
+            _stream_ptr(dev)))
+    return out_bytes, out_off, resp_out_len
+
+
+def new_stream_state(n_streams: int, device) -> torch.Tensor:
+    """Fresh per-stream state (depth 0, nothing held): uint8[n_streams, 32], layout of qb200_stream_state."""
+    st = torch.zeros((n_streams, STATE_BYTES), dtype=torch.uint8, device=device)
+    st[:, 4:8] = 0xFF  # tail_len = -1
+    return st
+
+
+def stream_feed_batch(tags: TagTable, chunk_bytes: torch.Tensor, chunk_off: torch.Tensor, stream_off: torch.Tensor,
+                      state: Optional[torch.Tensor] = None, *, flush: bool = False,
+                      state_out: Optional[torch.Tensor] = None, out_bytes: Optional[torch.Tensor] = None,
+                      out_chunk_off: Optional[torch.Tensor] = None, scratch: Optional[torch.Tensor] = None):
+    """ThinkingTagFilter.feed for every chunk of every stream, in order, state carried (qb200_stream_feed_batch).
+
+    chunk_bytes: uint8[total]; chunk_off: int64[n_chunks+1]; stream_off: int64[n_streams+1] (chunk indices).
+    state: uint8[n_streams, 32] from a previous call / new_stream_state, or None for fresh streams.
+    Returns (out_bytes, out_chunk_off, state_out): the feed of chunk c returned
+    out_bytes[out_chunk_off[c]:out_chunk_off[c+1]].
+    """
+    dev = chunk_off.device
+    _require_cuda(chunk_off, torch.int64, "chunk_off")
+    _require_cuda(stream_off, torch.int64, "stream_off")
+    _require_cuda(chunk_bytes, torch.uint8, "chunk_bytes")
+    n_chunks = chunk_off.numel() - 1
+    n_streams = stream_off.numel() - 1
+    if state is not None:
+        _require_cuda(state, torch.uint8, "state")
+        if state.numel() != n_streams * STATE_BYTES:
+            raise ValueError("state must be uint8[n_streams, 32]")
+    with torch.cuda.device(dev):
+        if out_bytes is None:
+            out_bytes = torch.empty(chunk_bytes.numel() + _lib.HELD_MAX * n_streams + 16, dtype=torch.uint8, device=dev)
+        if out_chunk_off is None:
+            out_chunk_off = torch.empty(n_chunks + 1, dtype=torch.int64, device=dev)
+        if state_out is None:
+            state_out = torch.empty((n_streams, STATE_BYTES), dtype=torch.uint8, device=dev)
+        need = lib().qb200_stream_feed_scratch_bytes(n_chunks, n_streams)
+        if scratch is None or scratch.numel() < need:
+            scratch = torch.empty(need, dtype=torch.uint8, device=dev)
+        check(lib().qb200_stream_feed_batch(
+            tags.handle, _ptr(chunk_bytes), _ptr(chunk_off), n_chunks, _ptr(stream_off), n_streams, _ptr(state),
+            _ptr(state_out), QB200_FLUSH if flush else 0, _ptr(out_bytes), out_bytes.numel(), _ptr(out_chunk_off),
+            _ptr(scratch), scratch.numel(), _stream_ptr(dev)))
+    return out_bytes, out_chunk_off, state_out
+
+
+def stream_flush_batch(state: torch.Tensor) -> torch.Tensor:
+    """ThinkingTagFilter.flush for every stream (oai_proxy.py:352-371): drops the held partial, keeps depth."""
+    _require_cuda(state, torch.uint8, "state")
+    with torch.cuda.device(state.device):
+        check(lib().qb200_stream_flush_batch(_ptr(state), state.numel() // STATE_BYTES, _stream_ptr(state.device)))
+    return state
+
+
+# ---- host <-> device packing helpers -----------------------------------------------------------------------------
+
+def pack_host(items: Sequence[bytes]) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Concatenate byte strings into pinned host tensors (uint8[total], int64[n+1])."""
+    lens = torch.tensor([len(b) for b in items], dtype=torch.int64)
+    off = torch.zeros(len(items) + 1, dtype=torch.int64)
+    torch.cumsum(lens, 0, out=off[1:])
+    total = int(off[-1])
+    data = torch.frombuffer(bytearray(b"".join(items)), dtype=torch.uint8) if total else torch.empty(0, dtype=torch.uint8)
+    if torch.cuda.is_available():
+        data, off = data.pin_memory(), off.pin_memory()
+    return data, off
+
+
+def split_host(out_bytes: torch.Tensor, out_off: torch.Tensor) -> List[bytes]:
+    """Device (or host) flat output -> list of bytes, one per offset interval."""
+    off = out_off.cpu().tolist()
+    raw = out_bytes[: off[-1]].cpu().numpy().tobytes() if off[-1] else b""
+    return [raw[off[i]:off[i + 1]] for i in range(len(off) - 1)]
+
+
+# ---- host-buffer sessions: the call a host application makes (pinned host memory in, pinned host memory out) -------
+
+class HostStreamFeeder:
+    """Reusable host-facing session for stream_feed_batch: device staging buffers and pinned result buffers are
+    allocated once for a maximum batch shape, every run() copies host -> device, runs the kernels, copies the released
+    bytes and per-chunk offsets device -> host."""
+
+    def __init__(self, tags: TagTable, device, max_bytes: int, max_chunks: int, max_streams: int):
+        self.tags, self.dev = tags, torch.device(device)
+        d = self.dev
+        self.d_data = torch.empty(max_bytes, dtype=torch.uint8, device=d)
+        self.d_co = torch.empty(max_chunks + 1, dtype=torch.int64, device=d)
+        self.d_so = torch.empty(max_streams + 1, dtype=torch.int64, device=d)
+        self.d_out = torch.empty(max_bytes + _lib.HELD_MAX * max_streams + 16, dtype=torch.uint8, device=d)
+        self.d_oco = torch.empty(max_chunks + 1, dtype=torch.int64, device=d)
+        self.d_state = new_stream_state(max_streams, d)
+        self.d_scratch = torch.empty(lib().qb200_stream_feed_scratch_bytes(max_chunks, max_streams), dtype=torch.uint8,
+                                     device=d)
+        self.h_out = torch.empty(self.d_out.numel(), dtype=torch.uint8).pin_memory()
+        self.h_oco = torch.empty(max_chunks + 1, dtype=torch.int64).pin_memory()
+
+    def run(self, h_data: torch.Tensor, h_chunk_off: torch.Tensor, h_stream_off: torch.Tensor, *, flush: bool,
+            carry_state: bool = False):
+        """Returns (h2d_bytes, d2h_bytes); results are in self.h_out[: self.h_oco[n_chunks]] and self.h_oco."""
+        nb, nc, ns = h_data.numel(), h_chunk_off.numel() - 1, h_stream_off.numel() - 1
+        data, co, so = self.d_data[:nb], self.d_co[:nc + 1], self.d_so[:ns + 1]
+        data.copy_(h_data, non_blocking=True)
+        co.copy_(h_chunk_off, non_blocking=True)
+        so.copy_(h_stream_off, non_blocking=True)
+        state = self.d_state[:ns]
+        stream_feed_batch(self.tags, data, co, so, state if carry_state else None, flush=flush, state_out=state,
+                          out_bytes=self.d_out, out_chunk_off=self.d_oco[:nc + 1], scratch=self.d_scratch)
+        self.h_oco[:nc + 1].copy_(self.d_oco[:nc + 1], non_blocking=True)
+        torch.cuda.current_stream(self.dev).synchronize()
+        total = int(self.h_oco[nc])
+        self.h_out[:total].copy_(self.d_out[:total], non_blocking=True)
+        torch.cuda.current_stream(self.dev).synchronize()
+        return nb + 8 * (nc + 1) + 8 * (ns + 1), total + 8 * (nc + 1)
+
+
+class HostStripConcat:
+    """Reusable host-facing session for strip_concat_batch (see HostStreamFeeder)."""
+
+    def __init__(self, tags: TagTable, device, max_bytes: int, max_resp: int, max_req: int, sep: bytes):
+        self.tags, self.dev = tags, torch.device(device)
+        d = self.dev
+        self.sep = torch.frombuffer(bytearray(sep), dtype=torch.uint8).to(d) if sep else None
+        self.d_data = torch.empty(max_bytes, dtype=torch.uint8, device=d)
+        self.d_io = torch.empty(max_resp + 1, dtype=torch.int64, device=d)
+        self.d_ro = torch.empty(max_req + 1, dtype=torch.int64, device=d)
+        self.d_out = torch.empty(max_bytes + len(sep) * max_resp + 16, dtype=torch.uint8, device=d)
+        self.d_oo = torch.empty(max_req + 1, dtype=torch.int64, device=d)
+        self.d_scratch = torch.empty(lib().qb200_strip_concat_scratch_bytes(max_resp, max_req), dtype=torch.uint8, device=d)
+        self.h_out = torch.empty(self.d_out.numel(), dtype=torch.uint8).pin_memory()
+        self.h_oo = torch.empty(max_req + 1, dtype=torch.int64).pin_memory()
+
+    def run(self, h_data: torch.Tensor, h_in_off: torch.Tensor, h_req_off: torch.Tensor, *, hide: bool, streaming: bool):
+        nb, nr, nq = h_data.numel(), h_in_off.numel() - 1, h_req_off.numel() - 1
+        data, io, ro = self.d_data[:nb], self.d_io[:nr + 1], self.d_ro[:nq + 1]
+        data.copy_(h_data, non_blocking=True)
+        io.copy_(h_in_off, non_blocking=True)
+        ro.copy_(h_req_off, non_blocking=True)
+        strip_concat_batch(self.tags, data, io, ro, self.sep, hide=hide, streaming=streaming, out_bytes=self.d_out,
+                           out_off=self.d_oo[:nq + 1], scratch=self.d_scratch)
+        self.h_oo[:nq + 1].copy_(self.d_oo[:nq + 1], non_blocking=True)
+        torch.cuda.current_stream(self.dev).synchronize()
+        total = int(self.h_oo[nq])
+        self.h_out[:total].copy_(self.d_out[:total], non_blocking=True)
+        torch.cuda.current_stream(self.dev).synchronize()
+        return nb + 8 * (nr + 1) + 8 * (nq + 1), total + 8 * (nq + 1)

@@ -1,0 +1,253 @@
+// Device-side building blocks shared by every kernel of the path: the tag table, tag / partial-tag matchers,
+// white-space classification, warp-level helpers.  Semantics follow SURVEY.md Appendix A; each function names the
+// reference lines (src/quorum/oai_proxy.py) whose behaviour it reproduces.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace qb {
+
+constexpr int kMaxTags = 16;
+constexpr int kNameStride = 24;
+constexpr int kHeldMax = 23;
+constexpr int kMaxCls = 128;
+constexpr unsigned kFull = 0xffffffffu;
+
+// Passed to kernels by value (__grid_constant__): no device allocation for the tag table.
+struct DevTags {
+    int32_t n;             // distinct lower-cased names (>= 1; an empty configured list gives one empty name)
+    int32_t hold_enabled;  // 0 when the configured list was empty (oai_proxy.py:301, 315 loop over nothing)
+    int32_t ncls;          // total backreference classes = sum over names of 2^(#i + #s letters)
+    int32_t pad;
+    uint8_t len[kMaxTags];
+    uint8_t cls_base[kMaxTags];
+    uint8_t name[kMaxTags][kNameStride];
+};
+
+struct StreamState {  // == qb200_stream_state
+    int32_t depth;
+    int32_t tail_len;
+    uint8_t held_len;
+    uint8_t held[kHeldMax];
+};
+static_assert(sizeof(StreamState) == 32, "state layout");
+
+// Byte accessors.  Positions are relative to the start of a unit (a response or a stream's data of this call).
+struct PtrAcc {
+    const uint8_t* p;
+    __device__ __forceinline__ uint8_t operator()(int64_t x) const { return p[x]; }
+};
+// Logical text = held bytes (positions -h .. -1) followed by the unit's bytes (positions 0 ..).
+struct HeldAcc {
+    const uint8_t* p;
+    const uint8_t* held;
+    int h;
+    __device__ __forceinline__ uint8_t operator()(int64_t x) const { return x < 0 ? held[h + x] : p[x]; }
+};
+
+// One pattern letter `pl` (lower-cased tag byte) against the text at x, text ends at `end`.
+// Returns bytes consumed (0 = no match).  var=1 when the text used U+0131 / U+017F (forms that only equal
+// themselves under the backreference); exotic=1 when it used a form str.lower() does not fold (U+0130, U+0131,
+// U+017F); cut=1 when a multi-byte form is cut by `end` (the prefix is still viable).
+// hold_fold=false: re.IGNORECASE (tag recognition, oai_proxy.py:139, 273-274);
+// hold_fold=true : candidate.lower() (hold-back test, oai_proxy.py:303, 317).
+template <class A>
+__device__ __forceinline__ int match_letter(const A& B, int64_t x, int64_t end, uint8_t pl, bool hold_fold, int& var,
+                                            int& exotic, int& cut) {
+    var = 0;
+    exotic = 0;
+    cut = 0;
+    if (x >= end) return 0;
+    uint8_t b = B(x);
+    if (pl >= 'a' && pl <= 'z') {
+        if (b == pl || b == (uint8_t)(pl - 32)) return 1;
+        if (pl == 'k' && b == 0xE2) {
+            if (x + 1 >= end) { cut = 1; return 0; }
+            if (B(x + 1) != 0x84) return 0;
+            if (x + 2 >= end) { cut = 1; return 0; }
+            return B(x + 2) == 0xAA ? 3 : 0;
+        }
+        if (!hold_fold && pl == 'i' && b == 0xC4) {
+            if (x + 1 >= end) { cut = 1; return 0; }
+            uint8_t c = B(x + 1);
+            if (c == 0xB0) { exotic = 1; return 2; }
+            if (c == 0xB1) { exotic = 1; var = 1; return 2; }
+            return 0;
+        }
+        if (!hold_fold && pl == 's' && b == 0xC5) {
+            if (x + 1 >= end) { cut = 1; return 0; }
+            if (B(x + 1) == 0xBF) { exotic = 1; var = 1; return 2; }
+            return 0;
+        }
+        return 0;
+    }
+    return b == pl ? 1 : 0;
+}
+
+// "<name>" (close=false) or "</name>" (close=true) starting at x and complete inside [x, end).
+// Returns the position after '>' or -1.  cls = dense backreference class (name, U+0131/U+017F variant mask);
+// exotic_pos = position of the first letter written in a form the hold-back fold rejects, or -1.
+template <class A>
+__device__ int64_t match_tag(const DevTags& tg, const A& B, int64_t x, int64_t end, bool close, int& cls,
+                             int64_t& exotic_pos) {
+    exotic_pos = -1;
+    if (x >= end || B(x) != '<') return -1;
+    int64_t q = x + 1;
+    if (close) {
+        if (q >= end || B(q) != '/') return -1;
+        q++;
+    }
+    for (int i = 0; i < tg.n; i++) {
+        int64_t r = q, ex = -1;
+        int mask = 0, bit = 0;
+        bool ok = true;
+        const int len = tg.len[i];
+        for (int k = 0; k < len; k++) {
+            uint8_t pl = tg.name[i][k];
+            int var, exo, cut;
+            int c = match_letter(B, r, end, pl, false, var, exo, cut);
+            if (!c) { ok = false; break; }
+            if (pl == 'i' || pl == 's') { mask |= var << bit; bit++; }
+            if (exo && ex < 0) ex = r;
+            r += c;
+        }
+        if (ok && r < end && B(r) == '>') {
+            cls = tg.cls_base[i] + mask;
+            exotic_pos = ex;
+            return r + 1;
+        }
+    }
+    return -1;
+}
+
+// Text [x, end) starts with '<' and is not a complete tag: is it a byte prefix of some complete tag?
+// hold_fold=true, allow_close=false : depth-0 hold-back test (oai_proxy.py:311-323)
+// hold_fold=false, allow_close=true : tail worth carrying inside a thinking block (oai_proxy.py:332-334)
+template <class A>
+__device__ bool is_tag_prefix(const DevTags& tg, const A& B, int64_t x, int64_t end, bool hold_fold, bool allow_close) {
+    if (x >= end || B(x) != '<') return false;
+    if (end - x > kHeldMax) return false;
+    for (int close = 0; close <= (allow_close ? 1 : 0); close++) {
+        int64_t q = x + 1;
+        if (close) {
+            if (q == end) return true;
+            if (B(q) != '/') continue;
+            q++;
+        }
+        for (int i = 0; i < tg.n; i++) {
+            int64_t r = q;
+            bool ok = true;
+            const int len = tg.len[i];
+            for (int k = 0; k < len; k++) {
+                if (r == end) break;
+                int var, exo, cut;
+                int c = match_letter(B, r, end, tg.name[i][k], hold_fold, var, exo, cut);
+                if (cut) return true;
+                if (!c) { ok = false; break; }
+                r += c;
+            }
+            if (ok && r == end) return true;
+        }
+    }
+    return false;
+}
+
+// Length of the str.isspace() code point that starts at p (0 if none); the sequence must fit in [p, end).
+template <class A>
+__device__ __forceinline__ int ws_len_at(const A& B, int64_t p, int64_t end) {
+    uint8_t c = B(p);
+    if ((c >= 0x09 && c <= 0x0D) || (c >= 0x1C && c <= 0x20)) return 1;
+    if (c < 0xC2 || c > 0xE3) return 0;
+    if (c == 0xC2) return (p + 1 < end && (B(p + 1) == 0x85 || B(p + 1) == 0xA0)) ? 2 : 0;
+    if (p + 2 < end) {
+        uint8_t d = B(p + 1), e = B(p + 2);
+        if (c == 0xE1) return (d == 0x9A && e == 0x80) ? 3 : 0;
+        if (c == 0xE2) {
+            if (d == 0x80 && ((e >= 0x80 && e <= 0x8A) || e == 0xA8 || e == 0xA9 || e == 0xAF)) return 3;
+            return (d == 0x81 && e == 0x9F) ? 3 : 0;
+        }
+        if (c == 0xE3) return (d == 0x80 && e == 0x80) ? 3 : 0;
+    }
+    return 0;
+}
+
+// Byte p of the text [0, n) belongs to a white-space code point (str.strip(), oai_proxy.py:139).
+template <class A>
+__device__ __forceinline__ bool is_white_byte(const A& B, int64_t p, int64_t n) {
+    uint8_t c = B(p);
+    if (c < 0x80) return (c >= 0x09 && c <= 0x0D) || (c >= 0x1C && c <= 0x20);
+#pragma unroll
+    for (int back = 0; back < 3; back++)
+        if (p - back >= 0 && ws_len_at(B, p - back, n) > back) return true;
+    return false;
+}
+
+// 4-bit mask of the bytes of w equal to '<'.
+__device__ __forceinline__ uint32_t lt_nibble(uint32_t w) {
+    uint32_t v = w ^ 0x3C3C3C3Cu;
+    uint32_t t = (v & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;
+    t = ~(t | v | 0x7F7F7F7Fu);        // 0x80 in every byte of v that is zero
+    return (t * 0x00204081u) >> 28;    // gather bits 7,15,23,31 -> 0..3
+}
+
+__device__ __forceinline__ uint32_t lt_mask16(uint4 v) {
+    return lt_nibble(v.x) | (lt_nibble(v.y) << 4) | (lt_nibble(v.z) << 8) | (lt_nibble(v.w) << 12);
+}
+
+// '<' bitmap of the 32-byte word `w` (absolute word index on the flat buffer `buf`, 16-byte aligned base,
+// `total` readable bytes).  Bit b <-> byte 32*w + b.
+__device__ __forceinline__ uint32_t load_lt_word(const uint8_t* buf, int64_t total, int64_t w) {
+    int64_t a = w << 5;
+    if (a + 32 <= total) {
+        const uint4* p = reinterpret_cast<const uint4*>(buf + a);
+        uint4 lo = __ldg(p), hi = __ldg(p + 1);
+        return lt_mask16(lo) | (lt_mask16(hi) << 16);
+    }
+    uint32_t m = 0;
+    for (int b = 0; b < 32 && a + b < total; b++)
+        if (buf[a + b] == '<') m |= 1u << b;
+    return m;
+}
+
+// bits b of a 32-byte word starting at unit-relative position wb whose position wb+b is >= p
+__device__ __forceinline__ uint32_t mask_ge(int64_t wb, int64_t p) {
+    int64_t d = p - wb;
+    return d <= 0 ? 0xffffffffu : (d >= 32 ? 0u : (0xffffffffu << (int)d));
+}
+
+// Warp-cooperative byte copy dst[0..n) = src[0..n).  16-byte stores on the aligned middle of dst; the source is read
+// as aligned 32-bit words and realigned with a funnel shift.  src_lo/src_hi bound what may be read.
+__device__ inline void warp_copy(uint8_t* dst, const uint8_t* src, int64_t n, const uint8_t* src_hi, int lane) {
+    if (n <= 0) return;
+    int64_t head = (16 - (reinterpret_cast<uintptr_t>(dst) & 15)) & 15;
+    if (head > n) head = n;
+    if (lane < head) dst[lane] = src[lane];
+    dst += head;
+    src += head;
+    n -= head;
+    int shift = (int)(reinterpret_cast<uintptr_t>(src) & 3);
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src - shift);
+    int64_t nvec = n >> 4;
+    // the realigning read touches 4 bytes past the vector when shift != 0: keep that inside [.., src_hi)
+    while (nvec > 0 && shift != 0 && reinterpret_cast<const uint8_t*>(s32 + 4 * nvec + 1) > src_hi) nvec--;
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+    for (int64_t v = lane; v < nvec; v += 32) {
+        const uint32_t* p = s32 + 4 * v;
+        uint32_t a0 = p[0], a1 = p[1], a2 = p[2], a3 = p[3];
+        uint4 o;
+        if (shift) {
+            uint32_t a4 = p[4];
+            int sh = shift * 8;
+            o.x = __funnelshift_r(a0, a1, sh);
+            o.y = __funnelshift_r(a1, a2, sh);
+            o.z = __funnelshift_r(a2, a3, sh);
+            o.w = __funnelshift_r(a3, a4, sh);
+        } else {
+            o = make_uint4(a0, a1, a2, a3);
+        }
+        d4[v] = o;
+    }
+    for (int64_t i = (nvec << 4) + lane; i < n; i += 32) dst[i] = src[i];
+}
+
+}  // namespace qb

@@ -1,0 +1,421 @@
+// quorum_b200 — kernels + C ABI (include/quorum_b200.h).  sm_100a only; no CPU fallback.
+//
+// General path ("warp per unit"): works for any unit size straight from global memory.
+//   strip_concat:  count kernel (filter + strip lengths)  ->  layout kernels (per-request prefix sums incl. separators)
+//                  ->  copy kernel (re-walk, vectorised copy to the final offsets)
+//   stream_feed :  count kernel (released bytes per stream) -> scan over streams -> copy kernel (bytes, per-chunk offsets,
+//                  carried state)
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <atomic>
+#include <new>
+
+#include "../../include/quorum_b200.h"
+#include "qb_walk.cuh"
+
+using namespace qb;
+
+struct qb200_tags {
+    DevTags dev;
+};
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+static int fail(int code, const char* fmt, const char* a = "") {
+    snprintf(g_err, sizeof(g_err), fmt, a);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                          \
+    do {                                                                        \
+        cudaError_t e_ = (expr);                                                \
+        if (e_ != cudaSuccess) return fail(QB200_ECUDA, "CUDA error: %s", cudaGetErrorString(e_)); \
+    } while (0)
+
+#define LAUNCHED() (g_launches.fetch_add(1, std::memory_order_relaxed))
+
+// ---------------------------------------------------------------------------------------------------------------
+// kernels: strip + concat
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kWarpsPerBlock = 8;
+constexpr int kThreads = kWarpsPerBlock * 32;
+
+// scratch layout for strip_concat: int64 klen[n_resp] | int64 first[n_resp] | int64 dst[n_resp] | int64 reqlen[n_req+1]
+__global__ void __launch_bounds__(kThreads)
+strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
+                   int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first) {
+    __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t total = in_off[n_resp];
+    for (int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib; r < n_resp; r += (int64_t)gridDim.x * kWarpsPerBlock) {
+        const int64_t a = in_off[r], b = in_off[r + 1];
+        StripWalker<false> w(tg, in, total, a, b - a, lastclose[wib], lane);
+        w.run();
+        if (lane == 0) {
+            klen[r] = w.res.kept_len;
+            first[r] = w.res.first_pos;
+        }
+        __syncwarp();
+    }
+}
+
+// one thread per request: relative offsets of its responses (separators included) and the request's total length
+__global__ void request_layout_kernel(const int64_t* __restrict__ in_off, const int64_t* __restrict__ req_off,
+                                      int64_t n_req, const int64_t* __restrict__ klen, int hide, int stream_join,
+                                      int32_t sep_len, int64_t* __restrict__ dst, int64_t* __restrict__ reqlen) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n_req) return;
+    const int64_t r0 = req_off ? req_off[q] : q, r1 = req_off ? req_off[q + 1] : q + 1;
+    int64_t o = 0;
+    bool first = true;
+    for (int64_t r = r0; r < r1; r++) {
+        const int64_t len = in_off[r + 1] - in_off[r];
+        if (stream_join && len == 0) {  // oai_proxy.py:763 `if text`
+            dst[r] = -1;
+            continue;
+        }
+        if (!first) o += sep_len;
+        first = false;
+        dst[r] = o;
+        o += hide ? klen[r] : len;
+    }
+    reqlen[q] = o;
+}
+
+// single-block exclusive scan of v[0..n) into out[0..n], out[n] = total
+__global__ void __launch_bounds__(1024) scan_kernel(const int64_t* __restrict__ v, int64_t n, int64_t* __restrict__ out) {
+    __shared__ int64_t warp_excl[32];
+    __shared__ int64_t block_total, carry_s;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (int64_t base = 0; base < n; base += 1024) {
+        const int64_t i = base + threadIdx.x;
+        const int64_t x = i < n ? v[i] : 0;
+        int64_t incl = x;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int64_t t = __shfl_up_sync(kFull, incl, d);
+            if (lane >= d) incl += t;
+        }
+        if (lane == 31) warp_excl[wid] = incl;
+        __syncthreads();
+        if (wid == 0) {
+            const int64_t ws = warp_excl[lane];
+            int64_t wi = ws;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int64_t t = __shfl_up_sync(kFull, wi, d);
+                if (lane >= d) wi += t;
+            }
+            warp_excl[lane] = wi - ws;
+            if (lane == 31) block_total = wi;
+        }
+        __syncthreads();
+        if (i < n) out[i] = carry_s + warp_excl[wid] + incl - x;
+        __syncthreads();
+        if (threadIdx.x == 0) carry_s += block_total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[n] = carry_s;
+}
+
+// dst[r] += out_off[request of r]   (thread per request)
+__global__ void request_finalize_kernel(const int64_t* __restrict__ req_off, int64_t n_req,
+                                        const int64_t* __restrict__ out_off, int64_t* __restrict__ dst) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n_req) return;
+    const int64_t r0 = req_off ? req_off[q] : q, r1 = req_off ? req_off[q + 1] : q + 1;
+    const int64_t base = out_off[q];
+    for (int64_t r = r0; r < r1; r++)
+        if (dst[r] >= 0) dst[r] += base;
+}
+
+__global__ void __launch_bounds__(kThreads)
+strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
+                  int64_t n_resp, const int64_t* __restrict__ klen, const int64_t* __restrict__ first,
+                  const int64_t* __restrict__ dst, int hide, const uint8_t* __restrict__ sep, int32_t sep_len,
+                  uint8_t* __restrict__ out, int64_t* __restrict__ resp_out_len) {
+    __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t total = in_off[n_resp];
+    for (int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib; r < n_resp; r += (int64_t)gridDim.x * kWarpsPerBlock) {
+        const int64_t a = in_off[r], b = in_off[r + 1];
+        const int64_t d = dst[r];
+        if (d < 0) {  // excluded from the join
+            if (resp_out_len && lane == 0) resp_out_len[r] = 0;
+            continue;
+        }
+        // a separator precedes every included response that is not the first included one of its request:
+        // request_layout_kernel left room for it right before dst[r]
+        const int64_t kl = hide ? klen[r] : (b - a);
+        if (resp_out_len && lane == 0) resp_out_len[r] = kl;
+        if (hide) {
+            StripWalker<true> w(tg, in, total, a, b - a, lastclose[wib], lane);
+            w.res.first_pos = first[r];
+            w.res.kept_len = kl;
+            w.dst = out + d;
+            if (kl > 0) w.run();
+        } else {
+            warp_copy(out + d, in + a, b - a, in + total, lane);
+        }
+        __syncwarp();
+    }
+}
+
+// separators: thread per response; writes sep right before dst[r] when r is not the first included response of its request
+__global__ void separator_kernel(const int64_t* __restrict__ req_off, int64_t n_req, const int64_t* __restrict__ dst,
+                                 const uint8_t* __restrict__ sep, int32_t sep_len, uint8_t* __restrict__ out) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n_req) return;
+    const int64_t r0 = req_off ? req_off[q] : q, r1 = req_off ? req_off[q + 1] : q + 1;
+    bool first = true;
+    for (int64_t r = r0; r < r1; r++) {
+        if (dst[r] < 0) continue;
+        if (!first)
+            for (int i = 0; i < sep_len; i++) out[dst[r] - sep_len + i] = sep[i];
+        first = false;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// kernels: stream feed
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
+                    const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
+                    int64_t n_streams, const StreamState* __restrict__ st_in, uint32_t flags,
+                    int64_t* __restrict__ totals) {
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t total = chunk_off[n_chunks];
+    for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
+        const int64_t c0 = stream_off[s], c1 = stream_off[s + 1];
+        StreamWalker<false> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags);
+        StreamResult r = w.run(st_in ? st_in + s : nullptr, nullptr);
+        if (lane == 0) totals[s] = r.total_out;
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+stream_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
+                   const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
+                   int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
+                   const int64_t* __restrict__ bases, uint8_t* __restrict__ out, int64_t* __restrict__ out_chunk_off) {
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t total = chunk_off[n_chunks];
+    for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
+        const int64_t c0 = stream_off[s], c1 = stream_off[s + 1];
+        StreamWalker<true> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags);
+        w.out_base = bases[s];
+        w.dst = out + bases[s];
+        w.out_chunk_off = out_chunk_off;
+        w.chunk0 = c0;
+        // state_in may alias state_out: the walker reads its input state before writing the output state
+        StreamState si;
+        if (st_in) si = st_in[s];
+        w.run(st_in ? &si : nullptr, st_out ? st_out + s : nullptr);
+        __syncwarp();
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n_streams == 0) out_chunk_off[0] = 0;
+}
+
+__global__ void stream_flush_kernel(StreamState* st, int64_t n) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) st[i].held_len = 0;
+}
+
+__global__ void set_i64_kernel(int64_t* p, int64_t v) { *p = v; }
+
+// ---------------------------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------------------------
+extern "C" {
+
+const char* qb200_last_error(void) { return g_err; }
+
+int64_t qb200_launch_count(void) { return g_launches.load(); }
+
+int qb200_tags_create(const uint8_t* names, const int32_t* name_off, int32_t n_tags, qb200_tags** out) {
+    if (!out || n_tags < 0 || (n_tags > 0 && (!names || !name_off))) return fail(QB200_EINVAL, "tags_create: bad argument");
+    qb200_tags* t = new (std::nothrow) qb200_tags();
+    if (!t) return fail(QB200_EINVAL, "tags_create: out of memory");
+    DevTags& d = t->dev;
+    memset(&d, 0, sizeof(d));
+    d.hold_enabled = n_tags > 0;
+    int ncls = 0;
+    for (int i = 0; i < n_tags; i++) {
+        int len = name_off[i + 1] - name_off[i];
+        if (len < 0 || len > QB200_MAX_TAG_LEN) { delete t; return fail(QB200_ETAGS, "tag name longer than QB200_MAX_TAG_LEN"); }
+        uint8_t low[kNameStride];
+        int worst = 2, nvar = 0;
+        for (int k = 0; k < len; k++) {
+            uint8_t c = names[name_off[i] + k];
+            if (c < 0x20 || c > 0x7E || strchr(".^$*+?{}[]\\|()<>/", c)) {
+                delete t;
+                return fail(QB200_ETAGS, "tag name must be printable ASCII without regex metacharacters or '<' '>' '/'");
+            }
+            if (c >= 'A' && c <= 'Z') c = (uint8_t)(c + 32);
+            low[k] = c;
+            worst += c == 'k' ? 3 : (c == 'i' || c == 's') ? 2 : 1;
+            nvar += (c == 'i' || c == 's');
+        }
+        if (worst > QB200_HELD_MAX) { delete t; return fail(QB200_ETAGS, "tag name too long: a partial tag would exceed QB200_HELD_MAX bytes"); }
+        bool dup = false;
+        for (int j = 0; j < d.n; j++)
+            if (d.len[j] == len && memcmp(d.name[j], low, (size_t)len) == 0) dup = true;
+        if (dup) continue;
+        if (d.n == QB200_MAX_TAGS) { delete t; return fail(QB200_ETAGS, "more than QB200_MAX_TAGS distinct tag names"); }
+        if (ncls + (1 << nvar) > kMaxCls) { delete t; return fail(QB200_ETAGS, "too many backreference classes (i/s letters)"); }
+        memcpy(d.name[d.n], low, (size_t)len);
+        d.len[d.n] = (uint8_t)len;
+        d.cls_base[d.n] = (uint8_t)ncls;
+        ncls += 1 << nvar;
+        d.n++;
+    }
+    if (d.n == 0) {  // "<()>": one empty name
+        d.n = 1;
+        d.len[0] = 0;
+        d.cls_base[0] = 0;
+        ncls = 1;
+    }
+    d.ncls = ncls;
+    *out = t;
+    return QB200_OK;
+}
+
+void qb200_tags_destroy(qb200_tags* tags) { delete tags; }
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req) {
+    if (n_resp < 0) n_resp = 0;
+    if (n_req < 0) n_req = 0;
+    return 3 * align256((size_t)(n_resp + 1) * 8) + align256((size_t)(n_req + 2) * 8) + 256;
+}
+
+static int grid_for(int64_t units) {
+    int64_t g = (units + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    const int64_t cap = 148 * 64;  // grid-stride beyond this
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, const int64_t* in_off, int64_t n_resp,
+                             const int64_t* req_off, int64_t n_req, const uint8_t* sep, int32_t sep_len, uint32_t flags,
+                             uint8_t* out_bytes, int64_t out_capacity, int64_t* out_off, int64_t* resp_out_len,
+                             void* scratch, size_t scratch_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!tags || !in_off || !out_off || n_resp < 0 || n_req < 0 || sep_len < 0 || (sep_len > 0 && !sep))
+        return fail(QB200_EINVAL, "strip_concat_batch: bad argument");
+    if (!req_off && n_req != n_resp) return fail(QB200_EINVAL, "strip_concat_batch: req_off == NULL needs n_req == n_resp");
+    if ((n_resp > 0 && (!in_bytes || !out_bytes)) || out_capacity < 0)
+        return fail(QB200_EINVAL, "strip_concat_batch: NULL data pointer");
+    if (((uintptr_t)in_bytes & 15) || ((uintptr_t)out_bytes & 15))
+        return fail(QB200_EINVAL, "strip_concat_batch: in_bytes/out_bytes must be 16-byte aligned");
+    if (scratch_bytes < qb200_strip_concat_scratch_bytes(n_resp, n_req) || !scratch)
+        return fail(QB200_ESCRATCH, "strip_concat_batch: scratch too small");
+    int dev_count = 0;
+    CUDA_TRY(cudaGetDeviceCount(&dev_count));
+    if (n_req == 0) {
+        set_i64_kernel<<<1, 1, 0, stream>>>(out_off, 0);
+        LAUNCHED();
+        CUDA_TRY(cudaGetLastError());
+        return QB200_OK;
+    }
+    uint8_t* sp = (uint8_t*)scratch;
+    int64_t* klen = (int64_t*)sp;
+    sp += align256((size_t)(n_resp + 1) * 8);
+    int64_t* first = (int64_t*)sp;
+    sp += align256((size_t)(n_resp + 1) * 8);
+    int64_t* dst = (int64_t*)sp;
+    sp += align256((size_t)(n_resp + 1) * 8);
+    int64_t* reqlen = (int64_t*)sp;
+    const int hide = (flags & QB200_HIDE) ? 1 : 0;
+    const int sj = (flags & QB200_STREAM_JOIN) ? 1 : 0;
+
+    if (hide && n_resp > 0) {
+        strip_count_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first);
+        LAUNCHED();
+    }
+    const int tb = 256;
+    const unsigned rg = (unsigned)((n_req + tb - 1) / tb);
+    request_layout_kernel<<<rg, tb, 0, stream>>>(in_off, req_off, n_req, klen, hide, sj, sep_len, dst, reqlen);
+    LAUNCHED();
+    scan_kernel<<<1, 1024, 0, stream>>>(reqlen, n_req, out_off);
+    LAUNCHED();
+    request_finalize_kernel<<<rg, tb, 0, stream>>>(req_off, n_req, out_off, dst);
+    LAUNCHED();
+    if (n_resp > 0) {
+        strip_copy_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, dst,
+                                                                    hide, sep, sep_len, out_bytes, resp_out_len);
+        LAUNCHED();
+    }
+    if (sep_len > 0 && req_off) {
+        separator_kernel<<<rg, tb, 0, stream>>>(req_off, n_req, dst, sep, sep_len, out_bytes);
+        LAUNCHED();
+    }
+    CUDA_TRY(cudaGetLastError());
+    return QB200_OK;
+}
+
+size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams) {
+    (void)n_chunks;
+    if (n_streams < 0) n_streams = 0;
+    return 2 * align256((size_t)(n_streams + 2) * 8) + 256;
+}
+
+int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
+                            const int64_t* stream_off, int64_t n_streams, const qb200_stream_state* state_in,
+                            qb200_stream_state* state_out, uint32_t flags, uint8_t* out_bytes, int64_t out_capacity,
+                            int64_t* out_chunk_off, void* scratch, size_t scratch_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!tags || !chunk_off || !stream_off || !out_chunk_off || n_chunks < 0 || n_streams < 0 || out_capacity < 0)
+        return fail(QB200_EINVAL, "stream_feed_batch: bad argument");
+    if (n_chunks > 0 && (!chunk_bytes || !out_bytes)) return fail(QB200_EINVAL, "stream_feed_batch: NULL data pointer");
+    if (((uintptr_t)chunk_bytes & 15) || ((uintptr_t)out_bytes & 15))
+        return fail(QB200_EINVAL, "stream_feed_batch: chunk_bytes/out_bytes must be 16-byte aligned");
+    if (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams) || !scratch)
+        return fail(QB200_ESCRATCH, "stream_feed_batch: scratch too small");
+    int dev_count = 0;
+    CUDA_TRY(cudaGetDeviceCount(&dev_count));
+    if (n_streams == 0) {
+        set_i64_kernel<<<1, 1, 0, stream>>>(out_chunk_off, 0);
+        LAUNCHED();
+        CUDA_TRY(cudaGetLastError());
+        return QB200_OK;
+    }
+    uint8_t* sp = (uint8_t*)scratch;
+    int64_t* totals = (int64_t*)sp;
+    sp += align256((size_t)(n_streams + 2) * 8);
+    int64_t* bases = (int64_t*)sp;
+    const StreamState* si = reinterpret_cast<const StreamState*>(state_in);
+    StreamState* so = reinterpret_cast<StreamState*>(state_out);
+    stream_count_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
+                                                                     n_streams, si, flags, totals);
+    LAUNCHED();
+    scan_kernel<<<1, 1024, 0, stream>>>(totals, n_streams, bases);
+    LAUNCHED();
+    stream_copy_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
+                                                                    n_streams, si, so, flags, bases, out_bytes, out_chunk_off);
+    LAUNCHED();
+    CUDA_TRY(cudaGetLastError());
+    return QB200_OK;
+}
+
+int qb200_stream_flush_batch(qb200_stream_state* state, int64_t n_streams, void* stream_) {
+    if (n_streams < 0 || (n_streams > 0 && !state)) return fail(QB200_EINVAL, "stream_flush_batch: bad argument");
+    if (n_streams == 0) return QB200_OK;
+    stream_flush_kernel<<<(unsigned)((n_streams + 255) / 256), 256, 0, (cudaStream_t)stream_>>>(
+        reinterpret_cast<StreamState*>(state), n_streams);
+    LAUNCHED();
+    CUDA_TRY(cudaGetLastError());
+    return QB200_OK;
+}
+
+}  // extern "C"

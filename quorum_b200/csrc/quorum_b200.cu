@@ -314,8 +314,7 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     if (!tags || !in_off || !out_off || n_resp < 0 || n_req < 0 || sep_len < 0 || (sep_len > 0 && !sep))
         return fail(QB200_EINVAL, "strip_concat_batch: bad argument");
     if (!req_off && n_req != n_resp) return fail(QB200_EINVAL, "strip_concat_batch: req_off == NULL needs n_req == n_resp");
-    if ((n_resp > 0 && (!in_bytes || !out_bytes)) || out_capacity < 0)
-        return fail(QB200_EINVAL, "strip_concat_batch: NULL data pointer");
+    if (out_capacity < 0) return fail(QB200_EINVAL, "strip_concat_batch: negative out_capacity");
     if (((uintptr_t)in_bytes & 15) || ((uintptr_t)out_bytes & 15))
         return fail(QB200_EINVAL, "strip_concat_batch: in_bytes/out_bytes must be 16-byte aligned");
     if (scratch_bytes < qb200_strip_concat_scratch_bytes(n_resp, n_req) || !scratch)
@@ -377,7 +376,6 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
     cudaStream_t stream = (cudaStream_t)stream_;
     if (!tags || !chunk_off || !stream_off || !out_chunk_off || n_chunks < 0 || n_streams < 0 || out_capacity < 0)
         return fail(QB200_EINVAL, "stream_feed_batch: bad argument");
-    if (n_chunks > 0 && (!chunk_bytes || !out_bytes)) return fail(QB200_EINVAL, "stream_feed_batch: NULL data pointer");
     if (((uintptr_t)chunk_bytes & 15) || ((uintptr_t)out_bytes & 15))
         return fail(QB200_EINVAL, "stream_feed_batch: chunk_bytes/out_bytes must be 16-byte aligned");
     if (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams) || !scratch)

@@ -223,11 +223,13 @@ struct StreamWalker {
             si.depth = 0;
             si.tail_len = -1;
             si.held_len = 0;
+            for (int i = 0; i < kHeldMax; i++) si.held[i] = 0;
         }
         StreamResult res{0};
         if (m <= 0) {  // nothing fed: state passes through
             if (COPY && st_out && lane == 0) {
                 if (flags & 4u) si.held_len = 0;
+                for (int i = si.held_len; i < kHeldMax; i++) si.held[i] = 0;
                 si.tail_len = -1;
                 *st_out = si;
             }
@@ -461,6 +463,7 @@ struct StreamWalker {
                     so.depth = depth;
                     so.tail_len = last_tok_end >= 0 ? (int32_t)(n - last_tok_end) : -1;
                     so.held_len = 0;
+                    for (int i = 0; i < kHeldMax; i++) so.held[i] = 0;  // unused bytes are defined (zero), not stale
                     if (hp != INT64_MIN) {
                         so.held_len = (uint8_t)(n - hp);
                         for (int i = 0; i < so.held_len; i++) so.held[i] = A(hp + i);

@@ -101,6 +101,24 @@ int qb200_stream_feed_batch(const qb200_tags *tags, const uint8_t *chunk_bytes, 
                             uint8_t *out_bytes, int64_t out_capacity, int64_t *out_chunk_off, void *scratch,
                             size_t scratch_bytes, void *stream);
 
+/* Same computation as qb200_stream_feed_batch for callers that cannot provide scratch memory.  No counterpart in the
+ * reference (it is a property of this library's deployment, not of quorum's algorithm).
+ * Meant for hosts that cannot allocate at call time: a process whose device memory is entirely pre-reserved by its
+ * own pools, a binding that owns only its input/output buffers, or a loop where cudaMalloc's device-wide
+ * synchronisation is not acceptable.  The scratch is a fixed array inside the library (about 1 MiB of device memory on
+ * every GPU that loads it, held until the process exits), so:
+ *   - at most QB200_NOALLOC_MAX_STREAMS streams per call (larger batches: QB200_EINVAL);
+ *   - all calls on one device share that array; calls that may overlap on the GPU race on it: serialise them;
+ *   - the first call on each device looks up the array's address (do it once, with that device current, before any
+ *     stream capture begins).
+ * The call itself performs no cudaMalloc / cudaFree and calls no allocating library routine.  Arguments and outputs are
+ * those of qb200_stream_feed_batch without `scratch` / `scratch_bytes`. */
+#define QB200_NOALLOC_MAX_STREAMS 65536
+int qb200_stream_feed_batch_noalloc(const qb200_tags *tags, const uint8_t *chunk_bytes, const int64_t *chunk_off,
+                                    int64_t n_chunks, const int64_t *stream_off, int64_t n_streams,
+                                    const qb200_stream_state *state_in, qb200_stream_state *state_out, uint32_t flags,
+                                    uint8_t *out_bytes, int64_t out_capacity, int64_t *out_chunk_off, void *stream);
+
 /* ThinkingTagFilter.flush for n streams without feeding (oai_proxy.py:352-371): drops the held partial, keeps depth. */
 int qb200_stream_flush_batch(qb200_stream_state *state, int64_t n_streams, void *stream);
 

@@ -15,8 +15,9 @@ STATE_BYTES = 32
 EXPORTS = [
     "qb200_last_error", "qb200_tags_create", "qb200_tags_destroy", "qb200_strip_concat_scratch_bytes",
     "qb200_strip_concat_batch", "qb200_stream_feed_scratch_bytes", "qb200_stream_feed_batch",
-    "qb200_stream_flush_batch", "qb200_launch_count",
+    "qb200_stream_flush_batch", "qb200_launch_count", "qb200_stream_feed_batch_noalloc",
 ]
+NOALLOC_MAX_STREAMS = 65536
 
 _lib = None
 
@@ -49,6 +50,8 @@ def lib() -> ctypes.CDLL:
     L.qb200_stream_feed_scratch_bytes.argtypes = [i64, i64]
     L.qb200_stream_feed_batch.restype = ctypes.c_int
     L.qb200_stream_feed_batch.argtypes = [vp, vp, vp, i64, vp, i64, vp, vp, u32, vp, i64, vp, vp, sz, vp]
+    L.qb200_stream_feed_batch_noalloc.restype = ctypes.c_int
+    L.qb200_stream_feed_batch_noalloc.argtypes = [vp, vp, vp, i64, vp, i64, vp, vp, u32, vp, i64, vp, vp]
     L.qb200_stream_flush_batch.restype = ctypes.c_int
     L.qb200_stream_flush_batch.argtypes = [vp, i64, vp]
     L.qb200_launch_count.restype = i64

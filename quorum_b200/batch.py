@@ -167,6 +167,30 @@ def stream_feed_batch(tags: TagTable, chunk_bytes: torch.Tensor, chunk_off: torc
     return out_bytes, out_chunk_off, state_out
 
 
+def stream_feed_batch_noalloc(tags: TagTable, chunk_bytes: torch.Tensor, chunk_off: torch.Tensor,
+                              stream_off: torch.Tensor, state: Optional[torch.Tensor], *, flush: bool,
+                              state_out: Optional[torch.Tensor], out_bytes: torch.Tensor,
+                              out_chunk_off: torch.Tensor) -> None:
+    """stream_feed_batch for hosts that must not allocate: every buffer, outputs included, is passed in by the caller and
+    this wrapper creates no tensor.  The library keeps its scratch in a fixed device array, so a call handles at most
+    `_lib.NOALLOC_MAX_STREAMS` streams, calls on one device must not overlap, and the first call on a device should be
+    made outside stream capture (qb200_stream_feed_batch_noalloc, include/quorum_b200.h)."""
+    dev = chunk_off.device
+    for t, dt, nm in ((chunk_off, torch.int64, "chunk_off"), (stream_off, torch.int64, "stream_off"),
+                      (chunk_bytes, torch.uint8, "chunk_bytes"), (out_bytes, torch.uint8, "out_bytes"),
+                      (out_chunk_off, torch.int64, "out_chunk_off")):
+        _require_cuda(t, dt, nm)
+    n_chunks = chunk_off.numel() - 1
+    n_streams = stream_off.numel() - 1
+    if out_chunk_off.numel() < n_chunks + 1:
+        raise ValueError("out_chunk_off needs n_chunks + 1 entries")
+    with torch.cuda.device(dev):
+        check(lib().qb200_stream_feed_batch_noalloc(
+            tags.handle, _ptr(chunk_bytes), _ptr(chunk_off), n_chunks, _ptr(stream_off), n_streams, _ptr(state),
+            _ptr(state_out), QB200_FLUSH if flush else 0, _ptr(out_bytes), out_bytes.numel(), _ptr(out_chunk_off),
+            _stream_ptr(dev)))
+
+
 def stream_flush_batch(state: torch.Tensor) -> torch.Tensor:
     """ThinkingTagFilter.flush for every stream (oai_proxy.py:352-371): drops the held partial, keeps depth."""
     _require_cuda(state, torch.uint8, "state")

@@ -406,6 +406,65 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
     return QB200_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of qb200_stream_feed_batch.
+//
+// Who needs it: a host that cannot hand over scratch memory at call time.  Examples: a serving process that gave all
+// of HBM to its own pools at start-up and has no allocator left to ask; a binding with nothing to allocate with (a
+// bare ctypes / cgo / JNI caller that only owns its input and output buffers); a latency-critical loop in which
+// cudaMalloc is forbidden because it synchronises the whole device and stalls every other stream.
+//
+// The scratch (two int64 arrays over the streams: released bytes per stream and their prefix sums) lives in the
+// file-scope device array below instead.  Consequences the caller must know:
+//   * the batch is limited to QB200_NOALLOC_MAX_STREAMS streams; more is rejected with QB200_EINVAL;
+//   * the array costs QB200_NOALLOC_SCRATCH_BYTES of device memory on every GPU that loads this library, until exit;
+//   * every call on a device uses the SAME array.  Two calls whose kernels can overlap on the GPU (different streams,
+//     different host threads) race on it and corrupt each other's offsets: serialise them.  The array still holds the
+//     previous call's values when a call starts; nothing in it has to start at zero, because the counting kernel
+//     overwrites every entry the later kernels read before they read it;
+//   * the first call on a device resolves the array's device address (set-up, once per device, with that device
+//     current).  Make that first call outside any stream capture.
+// ---------------------------------------------------------------------------------------------------------------
+#define QB200_NOALLOC_SCRATCH_BYTES_ (2 * (((QB200_NOALLOC_MAX_STREAMS + 2) * 8 + 255) / 256 * 256) + 256)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[QB200_NOALLOC_SCRATCH_BYTES_];
+
+static constexpr int kMaxDevices = 64;
+static std::atomic<void*> g_noalloc_ptr[kMaxDevices];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address: ask the runtime for the
+// address, on the device that is current, and cache it per device.
+static int noalloc_scratch_ptr(void** out) {
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail(QB200_EINVAL, "stream_feed_batch_noalloc: device ordinal out of range");
+    void* p = g_noalloc_ptr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(QB200_ECUDA, "stream_feed_batch_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+        g_noalloc_ptr[dev].store(p, std::memory_order_release);  // same value from every thread: a benign race
+    }
+    *out = p;
+    return QB200_OK;
+}
+
+int qb200_stream_feed_batch_noalloc(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off,
+                                    int64_t n_chunks, const int64_t* stream_off, int64_t n_streams,
+                                    const qb200_stream_state* state_in, qb200_stream_state* state_out, uint32_t flags,
+                                    uint8_t* out_bytes, int64_t out_capacity, int64_t* out_chunk_off, void* stream_) {
+    if (n_streams > QB200_NOALLOC_MAX_STREAMS)
+        return fail(QB200_EINVAL,
+                    "stream_feed_batch_noalloc: n_streams exceeds QB200_NOALLOC_MAX_STREAMS (65536); split the batch or "
+                    "use qb200_stream_feed_batch with caller-owned scratch");
+    void* scratch = nullptr;
+    int rc = noalloc_scratch_ptr(&scratch);
+    if (rc != QB200_OK) return rc;
+    // same kernels, same order as the allocating-caller entry point; only the scratch comes from the static array
+    return qb200_stream_feed_batch(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, state_in, state_out, flags,
+                                   out_bytes, out_capacity, out_chunk_off, scratch, (size_t)QB200_NOALLOC_SCRATCH_BYTES_,
+                                   stream_);
+}
+
 int qb200_stream_flush_batch(qb200_stream_state* state, int64_t n_streams, void* stream_) {
     if (n_streams < 0 || (n_streams > 0 && !state)) return fail(QB200_EINVAL, "stream_flush_batch: bad argument");
     if (n_streams == 0) return QB200_OK;

@@ -320,7 +320,7 @@ def main():
         out = torch.empty(total_in + 32 * n_units + 16, dtype=torch.uint8, device=dev)
         oco = torch.empty(n_items + 1, dtype=torch.int64, device=dev)
         state_out = torch.empty((n_units, 32), dtype=torch.uint8, device=dev)
-        scratch = torch.empty(qbatch.lib().qb200_stream_feed_scratch_bytes(n_items, n_units), dtype=torch.uint8, device=dev)
+        scratch = torch.empty(qbatch.lib().qb200_stream_feed_scratch_bytes(n_items, n_units, out.numel()), dtype=torch.uint8, device=dev)
 
         def step():
             qbatch.stream_feed_batch(table, data, chunk_off, stream_off, None, flush=True, state_out=state_out,

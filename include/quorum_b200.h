@@ -94,7 +94,7 @@ int qb200_strip_concat_batch(const qb200_tags *tags, const uint8_t *in_bytes, co
  * state_in == NULL starts every stream fresh (depth 0, nothing held); state_out may alias state_in or be NULL.
  * Outputs: the return value of the feed of chunk c is out_bytes[out_chunk_off[c] .. out_chunk_off[c+1])
  * (n_chunks+1 entries).  out_capacity must be >= chunk_off[n_chunks] + QB200_HELD_MAX * n_streams. */
-size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams);
+size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity);
 int qb200_stream_feed_batch(const qb200_tags *tags, const uint8_t *chunk_bytes, const int64_t *chunk_off,
                             int64_t n_chunks, const int64_t *stream_off, int64_t n_streams,
                             const qb200_stream_state *state_in, qb200_stream_state *state_out, uint32_t flags,

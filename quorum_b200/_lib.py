@@ -47,7 +47,7 @@ def lib() -> ctypes.CDLL:
     L.qb200_strip_concat_batch.restype = ctypes.c_int
     L.qb200_strip_concat_batch.argtypes = [vp, vp, vp, i64, vp, i64, vp, i32, u32, vp, i64, vp, vp, vp, sz, vp]
     L.qb200_stream_feed_scratch_bytes.restype = sz
-    L.qb200_stream_feed_scratch_bytes.argtypes = [i64, i64]
+    L.qb200_stream_feed_scratch_bytes.argtypes = [i64, i64, i64]
     L.qb200_stream_feed_batch.restype = ctypes.c_int
     L.qb200_stream_feed_batch.argtypes = [vp, vp, vp, i64, vp, i64, vp, vp, u32, vp, i64, vp, vp, sz, vp]
     L.qb200_stream_feed_batch_noalloc.restype = ctypes.c_int

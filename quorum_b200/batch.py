@@ -157,7 +157,7 @@ def stream_feed_batch(tags: TagTable, chunk_bytes: torch.Tensor, chunk_off: torc
             out_chunk_off = torch.empty(n_chunks + 1, dtype=torch.int64, device=dev)
         if state_out is None:
             state_out = torch.empty((n_streams, STATE_BYTES), dtype=torch.uint8, device=dev)
-        need = lib().qb200_stream_feed_scratch_bytes(n_chunks, n_streams)
+        need = lib().qb200_stream_feed_scratch_bytes(n_chunks, n_streams, out_bytes.numel())
         if scratch is None or scratch.numel() < need:
             scratch = torch.empty(need, dtype=torch.uint8, device=dev)
         check(lib().qb200_stream_feed_batch(
@@ -236,7 +236,7 @@ class HostStreamFeeder:
         self.d_out = torch.empty(max_bytes + _lib.HELD_MAX * max_streams + 16, dtype=torch.uint8, device=d)
         self.d_oco = torch.empty(max_chunks + 1, dtype=torch.int64, device=d)
         self.d_state = new_stream_state(max_streams, d)
-        self.d_scratch = torch.empty(lib().qb200_stream_feed_scratch_bytes(max_chunks, max_streams), dtype=torch.uint8,
+        self.d_scratch = torch.empty(lib().qb200_stream_feed_scratch_bytes(max_chunks, max_streams, self.d_out.numel()), dtype=torch.uint8,
                                      device=d)
         self.h_out = torch.empty(self.d_out.numel(), dtype=torch.uint8).pin_memory()
         self.h_oco = torch.empty(max_chunks + 1, dtype=torch.int64).pin_memory()

@@ -6,6 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "quorum_b200.cu")
 DEPS = [SRC, os.path.join(HERE, "csrc", "qb_common.cuh"), os.path.join(HERE, "csrc", "qb_walk.cuh"),
+        os.path.join(HERE, "csrc", "qb_tile.cuh"),
         os.path.join(os.path.dirname(HERE), "include", "quorum_b200.h")]
 LIB = os.path.join(HERE, "libquorum_b200.so")
 

@@ -200,7 +200,7 @@ __device__ __forceinline__ uint32_t load_lt_word(const uint8_t* buf, int64_t tot
     int64_t a = w << 5;
     if (a + 32 <= total) {
         const uint4* p = reinterpret_cast<const uint4*>(buf + a);
-        uint4 lo = __ldg(p), hi = __ldg(p + 1);
+        uint4 lo = p[0], hi = p[1];  // generic loads: the buffer may be global or shared memory
         return lt_mask16(lo) | (lt_mask16(hi) << 16);
     }
     uint32_t m = 0;

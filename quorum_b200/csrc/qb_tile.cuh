@@ -1,0 +1,813 @@
+// Fused single-pass tile kernels: every input byte is read from HBM once (TMA bulk copy into shared memory), every output
+// byte is written once, output offsets come from a decoupled look-back over tiles.
+//
+// Work assignment: the flat input is cut into 32 KiB windows; tile t owns the units (streams / responses) whose first
+// byte lies in window t, so units are never split and a tile's bytes are contiguous.  A CTA takes tiles from a ticket
+// counter (tiles start in index order, which the look-back needs for forward progress).
+//
+// Inside a tile (fast path, everything in shared memory):
+//   A  all warps, one 1 KiB step each: '<' bitmap (16-byte shared loads + SWAR), tag matching at the candidates
+//      against the tag table -> ordered token list (ballot/popc ranks + block scan of per-step counts)
+//   B  one warp per unit: sequential automaton over the (sparse) token list -> kept segments, kept bitmap painted
+//   C  block scan of kept-byte counts per word; one thread per feed boundary: release boundary + hold-back test
+//   D  block scan of per-unit output lengths, tile aggregate, decoupled look-back -> tile output base
+//   E  per-chunk offsets, carried state, and the kept segments copied out with 16-byte stores
+// A tile that does not fit the fast path's tables (too many units / tokens / segments / chunks, or a unit larger than
+// the staging buffer) runs the general warp-per-unit walkers of qb_walk.cuh inside the same kernel instead.
+#pragma once
+#include "qb_walk.cuh"
+
+namespace qb {
+
+constexpr int kWindow = 32768;            // bytes of input per tile window
+constexpr int kStageCap = 65536 + 64;     // staged bytes per tile: any unit <= 32 KiB that starts in the window fits
+constexpr int kTileWarps = 16;
+constexpr int kTileThreads = kTileWarps * 32;
+constexpr int kMaxSteps = (kStageCap + 1023) / 1024;
+constexpr int kStageWords = kMaxSteps * 32;
+constexpr int kMaxUnits = 64;
+constexpr int kTokCap = 640;
+constexpr int kSegCap = 320;
+constexpr int kChunkCap = 1088;
+constexpr int kSegPiece = 2048;           // long kept runs are split so the copy spreads over warps
+
+// ---------------------------------------------------------------------------------------------------------------
+// PTX helpers: mbarrier + TMA bulk copy (cp.async.bulk -> UBLKCP)
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Decoupled look-back over tiles (single pass prefix sum).  state word = status (2 bits) | value (62 bits).
+// Called by one full warp.  Returns the exclusive prefix of `aggregate` over all earlier tiles.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr unsigned long long kStAgg = 1ull << 62, kStPre = 2ull << 62, kStMask = (1ull << 62) - 1;
+
+__device__ inline int64_t lookback_exclusive(unsigned long long* tile_state, int64_t tile, int64_t aggregate, int lane) {
+    if (tile == 0) {
+        if (lane == 0) atomicExch(&tile_state[0], kStPre | (unsigned long long)aggregate);
+        return 0;
+    }
+    if (lane == 0) atomicExch(&tile_state[tile], kStAgg | (unsigned long long)aggregate);
+    int64_t excl = 0;
+    int64_t j = tile - 1;
+    for (;;) {
+        const int64_t idx = j - lane;
+        unsigned long long v = idx >= 0 ? ld_volatile_u64(&tile_state[idx]) : kStPre;
+        const unsigned st = (unsigned)(v >> 62);
+        const unsigned has_p = __ballot_sync(kFull, st == 2);
+        const unsigned inval = __ballot_sync(kFull, st == 0);
+        const int firstp = has_p ? __ffs(has_p) - 1 : 32;
+        const unsigned need = firstp >= 31 ? 0xffffffffu : ((2u << firstp) - 1u);
+        if (inval & need) continue;  // a predecessor has not published yet: poll again
+        int64_t val = (lane <= firstp) ? (int64_t)(v & kStMask) : 0;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(kFull, val, d);
+        excl += val;
+        if (has_p) break;
+        j -= 32;
+    }
+    if (lane == 0) atomicExch(&tile_state[tile], kStPre | (unsigned long long)(excl + aggregate));
+    return excl;
+}
+
+// Warp-cooperative lower bound: smallest u in [0, n] with start(u) >= key (start non-decreasing, start(n) = total).
+// `guess` narrows the first round when units are uniform.
+template <class F>
+__device__ inline int64_t warp_lower_bound(F start, int64_t n, int64_t key, int64_t guess, int lane) {
+    int64_t lo = 0, hi = n;
+    {   // probe 32 consecutive units around the guess
+        int64_t g0 = guess - 15;
+        if (g0 < 0) g0 = 0;
+        if (g0 > n) g0 = n;
+        const int64_t idx = g0 + lane;
+        const bool ge = idx >= n ? true : (start(idx) >= key);
+        const unsigned b = __ballot_sync(kFull, ge);
+        if (b == 0) {
+            lo = g0 + 32;
+        } else {
+            const int f = __ffs(b) - 1;
+            if (f > 0) return g0 + f;  // start(g0+f-1) < key <= start(g0+f)
+            hi = g0;                   // start(g0) >= key
+        }
+        if (lo > hi) lo = hi;
+    }
+    while (lo < hi) {
+        const int64_t span = hi - lo;
+        const int64_t step = (span + 31) / 32;
+        const int64_t idx = lo + (int64_t)lane * step;
+        const bool ge = idx >= hi ? true : (start(idx) >= key);
+        const unsigned b = __ballot_sync(kFull, ge);
+        if (b == 0) {  // every probe is below the key
+            lo = lo + 31 * step + 1;
+            continue;
+        }
+        const int f = __ffs(b) - 1;
+        if (f == 0) {
+            hi = lo;
+        } else {
+            const int64_t nlo = lo + (int64_t)(f - 1) * step + 1;
+            int64_t nhi = lo + (int64_t)f * step;
+            if (nhi > hi) nhi = hi;
+            lo = nlo;
+            hi = nhi;
+        }
+    }
+    return lo;
+}
+
+// token record: x = tile-relative position of '<';  y = len | close<<8 | cls<<9 | exrel<<16 (0xFF = no exotic form)
+struct Tok {
+    uint32_t x, y;
+};
+// kept segment: copy `len` bytes from tile-relative `src` to unit-relative output offset `dst`
+struct Seg {
+    uint32_t src, len, dst;
+    uint16_t unit, final_;
+};
+
+struct TileShared {
+    uint64_t mbar;
+    // tile geometry (written by warp 0)
+    int64_t g0;        // absolute offset of the first staged byte (multiple of 32)
+    int64_t u0, u1;    // unit range of this tile
+    int64_t c0;        // (streams) absolute index of the tile's first chunk
+    int64_t tile_base; // output offset of the tile
+    int32_t staged;    // staged bytes
+    int32_t nunits, nchunks, nsteps;
+    int32_t fast;      // 1 = fast path
+    int32_t ntok, nseg;
+    int32_t overflow;
+    unsigned long long agg;  // fallback: sum of unit totals
+    int32_t tile;
+    int32_t step_tok[kMaxSteps + 2];   // tokens per step -> exclusive offsets
+    int32_t step_cum[kMaxSteps + 2];   // kept bytes before the step
+    int32_t u_beg[kMaxUnits + 1], u_end[kMaxUnits + 1];       // tile-relative byte range
+    int32_t u_cend[kMaxUnits + 1];     // cumulative chunk count up to and including the unit (tile-local)
+    int32_t u_depth[kMaxUnits], u_last_tok_end[kMaxUnits], u_total[kMaxUnits], u_out_rel[kMaxUnits + 1];
+    int32_t u_rlast[kMaxUnits], u_gbeg[kMaxUnits];
+    uint8_t u_held_kept[kMaxUnits], u_held_unc[kMaxUnits];
+    Tok tok[kTokCap];
+    Seg seg[kSegCap];
+    int32_t bnd[kChunkCap];            // feed boundaries: tile-relative position, later (unit<<24 | released bytes before)
+    uint32_t ltbm[kStageWords];        // '<' bitmap, one word per 32 bytes
+    uint32_t keptbm[kStageWords];      // kept-byte bitmap
+    uint16_t wpre[kStageWords];        // kept bytes before the word inside its step
+    __align__(128) uint8_t data[kStageCap + 64];
+};
+
+// block-wide exclusive scan of one int per thread (kTileThreads threads); returns exclusive value, total via out param
+__device__ inline int block_excl_scan(int v, int* warp_tmp /* kTileWarps+1 ints in shared */, int& total) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(kFull, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) warp_tmp[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int ws = lane < kTileWarps ? warp_tmp[lane] : 0, wi = ws;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int t = __shfl_up_sync(kFull, wi, d);
+            if (lane >= d) wi += t;
+        }
+        if (lane < kTileWarps) warp_tmp[lane] = wi - ws;
+        if (lane == 31) warp_tmp[kTileWarps] = wi;
+    }
+    __syncthreads();
+    const int r = warp_tmp[wid] + incl - v;
+    total = warp_tmp[kTileWarps];
+    __syncthreads();
+    return r;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// stream feed, fused
+// ---------------------------------------------------------------------------------------------------------------
+struct StreamTileParams {
+    DevTags tg;
+    const uint8_t* bytes;
+    const int64_t* chunk_off;
+    int64_t n_chunks;
+    const int64_t* stream_off;
+    int64_t n_streams;
+    const StreamState* st_in;
+    StreamState* st_out;
+    uint32_t flags;
+    uint8_t* out;
+    int64_t* out_chunk_off;
+    unsigned long long* tile_state;  // [n_tiles], zeroed
+    unsigned int* ticket;            // zeroed
+    int64_t* unit_totals;            // [n_streams] scratch (fallback path)
+    int64_t* unit_bases;             // [n_streams] scratch (fallback path)
+    int64_t max_tiles;               // tiles the scratch has room for (>= total / kWindow + 1)
+};
+
+__global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __grid_constant__ StreamTileParams P) {
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    TileShared& S = *reinterpret_cast<TileShared*>(smem_raw);
+    __shared__ int scan_tmp[kTileWarps + 1];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const DevTags& tg = P.tg;
+    const int64_t total = P.chunk_off[P.n_chunks];
+    const int64_t n_tiles = total / kWindow + 1 <= P.max_tiles ? total / kWindow + 1 : P.max_tiles;
+    uint32_t parity = 0;
+    if (tid == 0) mbar_init(&S.mbar, 1);
+    __syncthreads();
+
+    auto ustart = [&](int64_t s) -> int64_t { return s >= P.n_streams ? total : P.chunk_off[P.stream_off[s]]; };
+
+    for (;;) {
+        // ---- take a tile ----
+        __syncthreads();
+        if (tid == 0) S.tile = (int32_t)atomicAdd(P.ticket, 1u);
+        __syncthreads();
+        const int64_t tile = S.tile;
+        if (tile >= n_tiles) break;
+
+        if (wid == 0) {
+            const int64_t w0 = tile * (int64_t)kWindow, w1 = w0 + kWindow;
+            const int64_t guess0 = total > 0 ? (int64_t)((double)w0 / (double)total * (double)P.n_streams) : 0;
+            const int64_t u0 = warp_lower_bound(ustart, P.n_streams, w0, guess0, lane);
+            const int64_t step_guess = P.n_streams > 0 && total > 0 ? (int64_t)((double)kWindow / ((double)total / (double)P.n_streams)) : 0;
+            int64_t u1 = (tile == n_tiles - 1) ? P.n_streams : warp_lower_bound(ustart, P.n_streams, w1, u0 + step_guess, lane);
+            if (u1 < u0) u1 = u0;
+            const int64_t b0 = ustart(u0), b1 = ustart(u1);
+            const int64_t g0 = b0 & ~(int64_t)31;
+            const int64_t nun = u1 - u0;
+            const int64_t c0 = u0 < P.n_streams ? P.stream_off[u0] : P.n_chunks;
+            const int64_t c1 = u1 < P.n_streams ? P.stream_off[u1] : P.n_chunks;
+            const bool fits = (b1 - g0) <= kStageCap;
+            if (lane == 0) {
+                S.g0 = g0;
+                S.u0 = u0;
+                S.u1 = u1;
+                S.c0 = c0;
+                S.nunits = (int32_t)(nun > 0x7fffffff ? 0x7fffffff : nun);
+                S.nchunks = (int32_t)((c1 - c0) > 0x7fffffff ? 0x7fffffff : (c1 - c0));
+                int64_t stg = fits ? (b1 - g0) : kStageCap;
+                if (g0 + stg > total) stg = total - g0;
+                S.staged = (int32_t)stg;
+                S.nsteps = (int32_t)((stg + 1023) >> 10);
+                S.fast = (fits && nun <= kMaxUnits && nun > 0 && (c1 - c0) <= kChunkCap) ? 1 : 0;
+                S.ntok = 0;
+                S.nseg = 0;
+                S.overflow = 0;
+                S.agg = 0;
+                // stage [g0, g0 + staged): TMA bulk copy of the 16-byte multiple, tail bytes by hand below
+                const uint32_t bulk = (uint32_t)(stg & ~(int64_t)15);
+                if (nun > 0 && bulk > 0) {
+                    fence_proxy_async();
+                    mbar_expect_tx(&S.mbar, bulk);
+                    uint32_t done = 0;
+                    while (done < bulk) {
+                        uint32_t n = bulk - done;
+                        if (n > 32768u) n = 32768u;
+                        bulk_g2s(S.data + done, P.bytes + g0 + done, n, &S.mbar);
+                        done += n;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        const int nunits = S.nunits;
+        if (nunits == 0) {
+            if (tile == 0 && tid == 0) P.out_chunk_off[0] = 0;
+            if (wid == 0) lookback_exclusive(P.tile_state, tile, 0, lane);
+            continue;
+        }
+        const int64_t g0 = S.g0;
+        const int staged = S.staged;
+        const bool fast = S.fast != 0;
+        // per-unit geometry + the tile's feed boundaries while the bulk copy is in flight
+        if (fast) {
+            for (int u = tid; u <= nunits; u += kTileThreads) {
+                const int64_t s = S.u0 + u;
+                const int64_t b = ustart(s);
+                const int64_t ce = (s < P.n_streams ? P.stream_off[s] : P.n_chunks) - S.c0;
+                if (u < nunits) S.u_beg[u] = (int32_t)(b - g0);
+                if (u > 0) {
+                    S.u_end[u - 1] = (int32_t)(b - g0);
+                    S.u_cend[u - 1] = (int32_t)ce;
+                }
+            }
+            for (int i = tid; i < S.nchunks; i += kTileThreads) S.bnd[i] = (int32_t)(P.chunk_off[S.c0 + 1 + i] - g0);
+            for (int i = tid; i < kStageWords; i += kTileThreads) S.keptbm[i] = 0;
+        }
+        // tail bytes the bulk copy could not take (size not a multiple of 16)
+        {
+            const int bulk = staged & ~15;
+            if (tid < staged - bulk) S.data[bulk + tid] = P.bytes[g0 + bulk + tid];
+            if ((staged & ~15) > 0) {
+                while (!mbar_try_wait(&S.mbar, parity)) {}
+            }
+        }
+        if ((staged & ~15) > 0) parity ^= 1;
+        __syncthreads();
+
+        if (fast) {
+            const int nsteps = S.nsteps;
+            const int lo_pos = S.u_beg[0], hi_pos = S.u_end[nunits - 1];
+            const PtrAcc D{S.data};
+            // unit containing tile-relative position x
+            auto unit_of = [&](int x) -> int {
+                int lo = 0, hi = nunits - 1;
+                while (lo < hi) {
+                    int mid = (lo + hi) >> 1;
+                    if (S.u_end[mid] > x) hi = mid;
+                    else lo = mid + 1;
+                }
+                return lo;
+            };
+            // ---- A: '<' bitmap and token masks, one step per warp at a time ----
+            uint32_t tokm[(kMaxSteps + kTileWarps - 1) / kTileWarps];
+#pragma unroll
+            for (int k = 0; k < (kMaxSteps + kTileWarps - 1) / kTileWarps; k++) {
+                tokm[k] = 0;
+                const int st = wid + k * kTileWarps;
+                if (st < nsteps) {
+                    const int wi = st * 32 + lane;
+                    const int wb = wi * 32;
+                    const uint4* p = reinterpret_cast<const uint4*>(S.data + wb);
+                    uint32_t lt = 0;
+                    if (wb < staged) {
+                        uint4 a = p[0], b = p[1];
+                        lt = lt_mask16(a) | (lt_mask16(b) << 16);
+                        lt &= mask_ge(wb, lo_pos) & ~mask_ge(wb, hi_pos);
+                    }
+                    S.ltbm[wi] = lt;
+                    uint32_t mm = lt, tk = 0;
+                    while (mm) {
+                        const int b = __ffs(mm) - 1;
+                        mm &= mm - 1;
+                        const int x = wb + b;
+                        const int ue = S.u_end[unit_of(x)];
+                        int cls;
+                        int64_t ex;
+                        if (match_tag(tg, D, x, ue, false, cls, ex) >= 0 || match_tag(tg, D, x, ue, true, cls, ex) >= 0)
+                            tk |= 1u << b;
+                    }
+                    tokm[k] = tk;
+                    int cnt = __popc(tk);
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(kFull, cnt, d);
+                    if (lane == 0) S.step_tok[st] = cnt;
+                }
+            }
+            __syncthreads();
+            {   // exclusive offsets of the steps' tokens
+                int v = tid < nsteps ? S.step_tok[tid] : 0, tot;
+                int e = block_excl_scan(v, scan_tmp, tot);
+                if (tid < nsteps) S.step_tok[tid] = e;
+                if (tid == 0) {
+                    S.ntok = tot;
+                    if (tot > kTokCap) S.overflow = 1;
+                }
+            }
+            __syncthreads();
+            if (!S.overflow) {
+#pragma unroll
+                for (int k = 0; k < (kMaxSteps + kTileWarps - 1) / kTileWarps; k++) {
+                    const int st = wid + k * kTileWarps;
+                    if (st < nsteps) {
+                        uint32_t tk = tokm[k];
+                        int pc = __popc(tk), incl = pc;
+#pragma unroll
+                        for (int d = 1; d < 32; d <<= 1) {
+                            int t = __shfl_up_sync(kFull, incl, d);
+                            if (lane >= d) incl += t;
+                        }
+                        int slot = S.step_tok[st] + incl - pc;
+                        const int wb = (st * 32 + lane) * 32;
+                        while (tk) {
+                            const int b = __ffs(tk) - 1;
+                            tk &= tk - 1;
+                            const int x = wb + b;
+                            const int ue = S.u_end[unit_of(x)];
+                            int cls;
+                            int64_t ex;
+                            int is_close = 0;
+                            int64_t tend = match_tag(tg, D, x, ue, false, cls, ex);
+                            if (tend < 0) {
+                                tend = match_tag(tg, D, x, ue, true, cls, ex);
+                                is_close = 1;
+                            }
+                            Tok t;
+                            t.x = (uint32_t)x;
+                            t.y = (uint32_t)(tend - x) | (is_close << 8) | (cls << 9) | ((ex >= 0 ? (uint32_t)(ex - x) : 0xFFu) << 16);
+                            S.tok[slot++] = t;
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        const bool fastok = fast && !S.overflow;
+
+        if (fastok) {
+            const int ntok = S.ntok;
+            // ---- B: one warp per unit walks its tokens (all lanes in lock step, state uniform) ----
+            for (int u = wid; u < nunits; u += kTileWarps) {
+                const int ub = S.u_beg[u], ue = S.u_end[u];
+                const int n = ue - ub;
+                const int64_t s = S.u0 + u;
+                const int64_t cfirst = P.stream_off[s];
+                const int64_t m = P.stream_off[s + 1] - cfirst;
+                const int64_t* co = P.chunk_off + cfirst;
+                const int64_t uabs = g0 + ub;
+                int32_t depth = 0;
+                int h = 0;
+                const uint8_t* heldp = S.data;
+                if (P.st_in) {
+                    depth = P.st_in[s].depth;
+                    h = P.st_in[s].held_len;
+                    heldp = P.st_in[s].held;
+                }
+                const HeldAcc A{S.data + ub, heldp, h};
+                int last_tok_end = -1, seg_start = 0, held_kept = 0, held_unc = 0, cum = 0;
+                auto first_boundary_after = [&](int64_t pos) -> int64_t {
+                    int64_t lo = 1, hi = m + 1;
+                    while (lo < hi) {
+                        int64_t mid = (lo + hi) >> 1;
+                        if (co[mid] - uabs > pos) hi = mid;
+                        else lo = mid + 1;
+                    }
+                    return lo;
+                };
+                auto recognised = [&](bool is_close, int64_t x, int64_t tend, int64_t ex) -> bool {
+                    if (is_close) return depth > 0;
+                    if (depth > 0) return true;
+                    if (tg.hold_enabled && ex < 0) return true;
+                    const int64_t lo = tg.hold_enabled ? ex : x;
+                    int64_t k = first_boundary_after(lo);
+                    return !(k <= m && co[k] - uabs < tend);
+                };
+                auto emit = [&](int sa, int sb, int fin) {  // kept run [sa, sb) in unit coordinates
+                    if (sb <= sa) return;
+                    // paint the kept bitmap
+                    const int a = ub + sa, b = ub + sb;
+                    const int w0 = a >> 5, w1 = (b - 1) >> 5;
+                    for (int w = w0 + lane; w <= w1; w += 32) {
+                        uint32_t msk = mask_ge(w * 32, a) & ~mask_ge(w * 32, b);
+                        if (msk == 0xffffffffu) S.keptbm[w] = msk;
+                        else atomicOr(&S.keptbm[w], msk);
+                    }
+                    // segment records, split into pieces
+                    const int len = sb - sa;
+                    const int npieces = (len + kSegPiece - 1) / kSegPiece;
+                    int slot = 0;
+                    if (lane == 0) slot = atomicAdd(&S.nseg, npieces);
+                    slot = __shfl_sync(kFull, slot, 0);
+                    if (slot + npieces > kSegCap) {
+                        S.overflow = 1;
+                    } else {
+                        for (int pi = lane; pi < npieces; pi += 32) {
+                            Seg sg;
+                            sg.src = (uint32_t)(a + pi * kSegPiece);
+                            sg.len = (uint32_t)((pi == npieces - 1) ? len - pi * kSegPiece : kSegPiece);
+                            sg.dst = (uint32_t)(cum + pi * kSegPiece);
+                            sg.unit = (uint16_t)u;
+                            sg.final_ = (uint16_t)fin;
+                            S.seg[slot + pi] = sg;
+                        }
+                    }
+                    cum += len;
+                };
+                if (m > 0) {
+                    if (h > 0) {  // the carried partial tag
+                        int cls;
+                        int64_t ex;
+                        int64_t tend = match_tag(tg, A, -h, n, false, cls, ex);
+                        bool is_close = false;
+                        if (tend < 0 && depth > 0) {
+                            tend = match_tag(tg, A, -h, n, true, cls, ex);
+                            is_close = true;
+                        }
+                        if (tend >= 0 && recognised(is_close, -h, tend, ex)) {
+                            depth += is_close ? -1 : 1;
+                            last_tok_end = seg_start = (int)tend;
+                        } else {
+                            held_unc = 1;
+                            if (depth == 0) held_kept = h;
+                        }
+                    }
+                    cum = held_kept;
+                    // tokens of this unit: [t0, t1)
+                    int t0, t1;
+                    {
+                        int lo = 0, hi = ntok;
+                        while (lo < hi) {
+                            int mid = (lo + hi) >> 1;
+                            if ((int)S.tok[mid].x >= ub) hi = mid;
+                            else lo = mid + 1;
+                        }
+                        t0 = lo;
+                        hi = ntok;
+                        while (lo < hi) {
+                            int mid = (lo + hi) >> 1;
+                            if ((int)S.tok[mid].x >= ue) hi = mid;
+                            else lo = mid + 1;
+                        }
+                        t1 = lo;
+                    }
+                    for (int t = t0; t < t1; t++) {
+                        const Tok tk = S.tok[t];
+                        const int x = (int)tk.x - ub;
+                        const int tend = x + (int)(tk.y & 0xff);
+                        const bool is_close = (tk.y >> 8) & 1;
+                        const int exr = (tk.y >> 16) & 0xff;
+                        const int64_t ex = exr == 0xff ? -1 : x + exr;
+                        if (recognised(is_close, x, tend, ex)) {
+                            if (depth == 0) {
+                                emit(seg_start, x, 0);
+                                depth = 1;
+                            } else {
+                                depth += is_close ? -1 : 1;
+                                if (depth == 0) seg_start = tend;
+                            }
+                            last_tok_end = tend;
+                        }
+                    }
+                    if (depth == 0) emit(seg_start, n, 1);
+                }
+                if (lane == 0) {
+                    S.u_depth[u] = depth;
+                    S.u_last_tok_end[u] = last_tok_end;
+                    S.u_held_kept[u] = (uint8_t)held_kept;
+                    S.u_held_unc[u] = (uint8_t)held_unc;
+                }
+            }
+            __syncthreads();
+        }
+        const bool fastok2 = fastok && !S.overflow;
+
+        if (fastok2) {
+            const int nsteps = S.nsteps;
+            // ---- C: kept bytes before every word (step_cum + wpre), then one thread per feed boundary ----
+            for (int st = wid; st < nsteps; st += kTileWarps) {
+                const int wi = st * 32 + lane;
+                const int pc = __popc(S.keptbm[wi]);
+                int incl = pc;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    int t = __shfl_up_sync(kFull, incl, d);
+                    if (lane >= d) incl += t;
+                }
+                S.wpre[wi] = (uint16_t)(incl - pc);
+                if (lane == 31) S.step_cum[st] = incl;
+            }
+            __syncthreads();
+            {
+                int v = tid < nsteps ? S.step_cum[tid] : 0, tot;
+                int e = block_excl_scan(v, scan_tmp, tot);
+                if (tid < nsteps) S.step_cum[tid] = e;
+                if (tid == 0) S.step_cum[nsteps] = tot;
+            }
+            __syncthreads();
+            auto G = [&](int x) -> int {  // kept bytes in tile positions [0, x)
+                const int w = x >> 5, b = x & 31;
+                if ((w >> 5) >= nsteps) return S.step_cum[nsteps];
+                return S.step_cum[w >> 5] + S.wpre[w] + (b ? __popc(S.keptbm[w] & ((1u << b) - 1u)) : 0);
+            };
+            for (int u = tid; u < nunits; u += kTileThreads) {
+                S.u_gbeg[u] = G(S.u_beg[u]);
+                S.u_rlast[u] = 0;
+                S.u_total[u] = 0;
+            }
+            __syncthreads();
+            const int nb = S.nchunks;
+            for (int i = tid; i < nb; i += kTileThreads) {
+                const int cpos = S.bnd[i];
+                // unit of boundary i: first unit with u_cend > i
+                int lo = 0, hi = nunits - 1;
+                while (lo < hi) {
+                    int mid = (lo + hi) >> 1;
+                    if (S.u_cend[mid] > i) hi = mid;
+                    else lo = mid + 1;
+                }
+                const int u = lo;
+                const int ub = S.u_beg[u];
+                const int c = cpos - ub;  // unit coordinates
+                const int hk = S.u_held_kept[u];
+                int Pv = hk + G(cpos) - S.u_gbeg[u], R = c;
+                bool found_lt = false;
+                if (c > 0) {
+                    const int w = (cpos - 1) >> 5;
+                    const int nbits = cpos - w * 32;  // 1..32
+                    const uint32_t low = nbits >= 32 ? 0xffffffffu : ((1u << nbits) - 1u);
+                    const uint32_t ltw = S.ltbm[w] & low & mask_ge(w * 32, ub);
+                    int p = 0;
+                    bool p_kept = false;
+                    if (ltw) {
+                        const int b = 31 - __clz(ltw);
+                        p = w * 32 + b;
+                        p_kept = (S.keptbm[w] >> b) & 1u;
+                        found_lt = true;
+                    } else if (w > 0) {
+                        const uint32_t ltp = S.ltbm[w - 1] & mask_ge((w - 1) * 32, ub);
+                        if (ltp) {
+                            const int b = 31 - __clz(ltp);
+                            p = (w - 1) * 32 + b;
+                            p_kept = (S.keptbm[w - 1] >> b) & 1u;
+                            found_lt = true;
+                        }
+                    }
+                    if (found_lt && p_kept && tg.hold_enabled && cpos - p <= kHeldMax &&
+                        is_tag_prefix(tg, PtrAcc{S.data}, p, cpos, true, false)) {
+                        R = p - ub;
+                        Pv -= (cpos - p);
+                    }
+                }
+                if (!found_lt && hk) {
+                    const int64_t s = S.u0 + u;
+                    const int h = P.st_in[s].held_len;
+                    if (tg.hold_enabled && c + h <= kHeldMax &&
+                        is_tag_prefix(tg, HeldAcc{S.data + ub, P.st_in[s].held, h}, -h, c, true, false)) {
+                        R = -h;
+                        Pv = 0;
+                    }
+                }
+                S.bnd[i] = (u << 24) | Pv;
+                if (i == S.u_cend[u] - 1) {  // the unit's last feed boundary
+                    S.u_rlast[u] = R;
+                    S.u_total[u] = Pv;
+                }
+            }
+            __syncthreads();
+            // ---- D: unit output offsets inside the tile, tile aggregate, look-back ----
+            {
+                int v = tid < nunits ? S.u_total[tid] : 0, tot;
+                int e = block_excl_scan(v, scan_tmp, tot);
+                if (tid < nunits) S.u_out_rel[tid] = e;
+                if (wid == 0) {
+                    int64_t base = lookback_exclusive(P.tile_state, tile, tot, lane);
+                    if (lane == 0) S.tile_base = base;
+                }
+            }
+            __syncthreads();
+            // ---- E: offsets, state, bytes ----
+            const int64_t tbase = S.tile_base;
+            if (tile == 0 && tid == 0) P.out_chunk_off[0] = 0;
+            for (int i = tid; i < nb; i += kTileThreads) {
+                const int v = S.bnd[i];
+                P.out_chunk_off[S.c0 + 1 + i] = tbase + S.u_out_rel[v >> 24] + (v & 0xffffff);
+            }
+            for (int u = tid; u < nunits; u += kTileThreads) {
+                const int64_t s = S.u0 + u;
+                const int ub = S.u_beg[u], n = S.u_end[u] - ub;
+                const int64_t m = P.stream_off[s + 1] - P.stream_off[s];
+                StreamState si;
+                if (P.st_in) {
+                    si = P.st_in[s];
+                } else {
+                    si.depth = 0;
+                    si.tail_len = -1;
+                    si.held_len = 0;
+                    for (int k = 0; k < kHeldMax; k++) si.held[k] = 0;
+                }
+                const int h = si.held_len;
+                StreamState so;
+                if (m == 0) {
+                    so = si;
+                    if (P.flags & 4u) so.held_len = 0;
+                    for (int k = so.held_len; k < kHeldMax; k++) so.held[k] = 0;
+                    so.tail_len = -1;
+                } else {
+                    const HeldAcc A{S.data + ub, si.held, h};
+                    const int depth = S.u_depth[u], lte = S.u_last_tok_end[u], rl = S.u_rlast[u];
+                    // carried literal bytes come first in the unit's output
+                    if (S.u_held_kept[u] && rl > -h) {
+                        uint8_t* d = P.out + tbase + S.u_out_rel[u];
+                        for (int k = 0; k < h; k++) d[k] = si.held[k];
+                    }
+                    int hp = INT32_MIN;
+                    if (!(P.flags & 4u)) {
+                        if (depth == 0) {
+                            if (rl < n) hp = rl;
+                        } else {
+                            int lo = n - kHeldMax;
+                            if (lo < 0) lo = 0;
+                            if (lte > lo) lo = lte;
+                            int p = INT32_MIN;
+                            for (int x = n - 1; x >= lo; x--)
+                                if (S.data[ub + x] == '<') { p = x; break; }
+                            if (p == INT32_MIN && S.u_held_unc[u] && lte < 0 && n + h <= kHeldMax) p = -h;
+                            if (p != INT32_MIN && is_tag_prefix(tg, A, p, n, false, true)) hp = p;
+                        }
+                    }
+                    so.depth = depth;
+                    so.tail_len = lte >= 0 ? (n - lte) : -1;
+                    so.held_len = 0;
+                    for (int k = 0; k < kHeldMax; k++) so.held[k] = 0;
+                    if (hp != INT32_MIN) {
+                        so.held_len = (uint8_t)(n - hp);
+                        for (int k = 0; k < so.held_len; k++) so.held[k] = A(hp + k);
+                    }
+                }
+                if (P.st_out) P.st_out[s] = so;
+            }
+            const int nseg = S.nseg;
+            for (int i = wid; i < nseg; i += kTileWarps) {
+                const Seg sg = S.seg[i];
+                const int u = sg.unit;
+                int len = (int)sg.len;
+                if (sg.final_) {  // the unit's last kept run is clipped at the last release boundary
+                    const int lim = S.u_beg[u] + S.u_rlast[u] - (int)sg.src;
+                    if (lim < len) len = lim;
+                }
+                if (len > 0)
+                    warp_copy(P.out + tbase + S.u_out_rel[u] + sg.dst, S.data + sg.src, len, S.data + kStageCap + 64, lane);
+            }
+        } else {
+            // ---- general path inside the tile: warp-per-unit walkers, from shared memory when the unit is staged ----
+            const int64_t u0 = S.u0, u1 = S.u1;
+            const uint8_t* sbuf = S.data - g0;  // so that sbuf + absolute offset addresses the staged copy
+            for (int64_t s = u0 + wid; s < u1; s += kTileWarps) {
+                const int64_t cf = P.stream_off[s], m = P.stream_off[s + 1] - cf;
+                const int64_t ua = P.chunk_off[cf], ub_ = P.chunk_off[cf + m];
+                const bool in_smem = ub_ - g0 <= staged;
+                StreamWalker<false> w(tg, in_smem ? sbuf : P.bytes, in_smem ? g0 + staged : total, P.chunk_off + cf, m, lane,
+                                      P.flags);
+                (void)ua;
+                StreamResult r = w.run(P.st_in ? P.st_in + s : nullptr, nullptr);
+                if (lane == 0) {
+                    P.unit_totals[s] = r.total_out;
+                    atomicAdd(&S.agg, (unsigned long long)r.total_out);
+                }
+                __syncwarp();
+            }
+            __syncthreads();
+            if (wid == 0) {
+                int64_t base = lookback_exclusive(P.tile_state, tile, (int64_t)S.agg, lane);
+                if (lane == 0) S.tile_base = base;
+            }
+            // exclusive offsets of the tile's units (kept in global scratch: the unit count is unbounded here)
+            if (wid == 1) {
+                int64_t run = 0;
+                for (int64_t b = u0; b < u1; b += 32) {
+                    const int64_t s = b + lane;
+                    const int64_t v = s < u1 ? P.unit_totals[s] : 0;
+                    int64_t incl = v;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        int64_t t = __shfl_up_sync(kFull, incl, d);
+                        if (lane >= d) incl += t;
+                    }
+                    if (s < u1) P.unit_bases[s] = run + incl - v;
+                    run += __shfl_sync(kFull, incl, 31);
+                }
+            }
+            __threadfence_block();
+            __syncthreads();
+            const int64_t tbase = S.tile_base;
+            if (tile == 0 && tid == 0) P.out_chunk_off[0] = 0;
+            for (int64_t s = u0 + wid; s < u1; s += kTileWarps) {
+                const int64_t cf = P.stream_off[s], m = P.stream_off[s + 1] - cf;
+                const int64_t ub_ = P.chunk_off[cf + m];
+                const bool in_smem = ub_ - g0 <= staged;
+                StreamWalker<true> w(tg, in_smem ? sbuf : P.bytes, in_smem ? g0 + staged : total, P.chunk_off + cf, m, lane,
+                                     P.flags);
+                w.out_base = tbase + P.unit_bases[s];
+                w.dst = P.out + w.out_base;
+                w.out_chunk_off = P.out_chunk_off;
+                w.chunk0 = cf;
+                StreamState si;
+                if (P.st_in) si = P.st_in[s];
+                w.run(P.st_in ? &si : nullptr, P.st_out ? P.st_out + s : nullptr);
+                __syncwarp();
+            }
+        }
+    }
+}
+
+}  // namespace qb

@@ -15,6 +15,8 @@
 
 #include "../../include/quorum_b200.h"
 #include "qb_walk.cuh"
+#include "qb_tile.cuh"
+#include <stdlib.h>
 
 using namespace qb;
 
@@ -363,25 +365,45 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     return QB200_OK;
 }
 
-size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams) {
-    (void)n_chunks;
+static size_t stream_general_scratch_bytes(int64_t n_streams) {
     if (n_streams < 0) n_streams = 0;
     return 2 * align256((size_t)(n_streams + 2) * 8) + 256;
 }
 
-int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
-                            const int64_t* stream_off, int64_t n_streams, const qb200_stream_state* state_in,
-                            qb200_stream_state* state_out, uint32_t flags, uint8_t* out_bytes, int64_t out_capacity,
-                            int64_t* out_chunk_off, void* scratch, size_t scratch_bytes, void* stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
+static int64_t tiles_for(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte_bound) / kWindow + 2; }
+
+size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity) {
+    (void)n_chunks;
+    return stream_general_scratch_bytes(n_streams) + align256((size_t)(tiles_for(out_capacity) + 1) * 8) + 256;
+}
+
+static bool force_general() {
+    const char* e = getenv("QB200_PATH");
+    return e && strcmp(e, "general") == 0;
+}
+
+static int stream_feed_check(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
+                             const int64_t* stream_off, int64_t n_streams, uint8_t* out_bytes, int64_t out_capacity,
+                             int64_t* out_chunk_off) {
     if (!tags || !chunk_off || !stream_off || !out_chunk_off || n_chunks < 0 || n_streams < 0 || out_capacity < 0)
         return fail(QB200_EINVAL, "stream_feed_batch: bad argument");
     if (((uintptr_t)chunk_bytes & 15) || ((uintptr_t)out_bytes & 15))
         return fail(QB200_EINVAL, "stream_feed_batch: chunk_bytes/out_bytes must be 16-byte aligned");
-    if (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams) || !scratch)
-        return fail(QB200_ESCRATCH, "stream_feed_batch: scratch too small");
     int dev_count = 0;
     CUDA_TRY(cudaGetDeviceCount(&dev_count));
+    return QB200_OK;
+}
+
+// General path: count kernel -> scan over streams -> copy kernel.  Any unit size, input read twice.
+static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
+                               const int64_t* stream_off, int64_t n_streams, const qb200_stream_state* state_in,
+                               qb200_stream_state* state_out, uint32_t flags, uint8_t* out_bytes, int64_t out_capacity,
+                               int64_t* out_chunk_off, void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+    int rc = stream_feed_check(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, out_bytes, out_capacity,
+                               out_chunk_off);
+    if (rc != QB200_OK) return rc;
+    if (scratch_bytes < stream_general_scratch_bytes(n_streams) || !scratch)
+        return fail(QB200_ESCRATCH, "stream_feed_batch: scratch too small");
     if (n_streams == 0) {
         set_i64_kernel<<<1, 1, 0, stream>>>(out_chunk_off, 0);
         LAUNCHED();
@@ -401,6 +423,65 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
     LAUNCHED();
     stream_copy_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
                                                                     n_streams, si, so, flags, bases, out_bytes, out_chunk_off);
+    LAUNCHED();
+    CUDA_TRY(cudaGetLastError());
+    return QB200_OK;
+}
+
+static int g_sm_count = 0;
+static int sm_count() {
+    if (!g_sm_count) {
+        int dev = 0, n = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        g_sm_count = n > 0 ? n : 148;
+    }
+    return g_sm_count;
+}
+
+int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
+                            const int64_t* stream_off, int64_t n_streams, const qb200_stream_state* state_in,
+                            qb200_stream_state* state_out, uint32_t flags, uint8_t* out_bytes, int64_t out_capacity,
+                            int64_t* out_chunk_off, void* scratch, size_t scratch_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (force_general() || n_streams == 0)
+        return stream_feed_general(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, state_in, state_out, flags,
+                                   out_bytes, out_capacity, out_chunk_off, scratch, scratch_bytes, stream);
+    int rc = stream_feed_check(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, out_bytes, out_capacity,
+                               out_chunk_off);
+    if (rc != QB200_OK) return rc;
+    if (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams, out_capacity) || !scratch)
+        return fail(QB200_ESCRATCH, "stream_feed_batch: scratch too small (see qb200_stream_feed_scratch_bytes)");
+    // Fused single-pass path.  scratch: totals | bases (general walkers inside the kernel) | tile states + ticket (zeroed)
+    uint8_t* sp = (uint8_t*)scratch;
+    StreamTileParams P;
+    P.tg = tags->dev;
+    P.bytes = chunk_bytes;
+    P.chunk_off = chunk_off;
+    P.n_chunks = n_chunks;
+    P.stream_off = stream_off;
+    P.n_streams = n_streams;
+    P.st_in = reinterpret_cast<const StreamState*>(state_in);
+    P.st_out = reinterpret_cast<StreamState*>(state_out);
+    P.flags = flags;
+    P.out = out_bytes;
+    P.out_chunk_off = out_chunk_off;
+    P.unit_totals = (int64_t*)sp;
+    sp += align256((size_t)(n_streams + 2) * 8);
+    P.unit_bases = (int64_t*)sp;
+    sp += align256((size_t)(n_streams + 2) * 8);
+    const int64_t max_tiles = tiles_for(out_capacity);
+    P.tile_state = (unsigned long long*)sp;
+    P.ticket = (unsigned int*)(P.tile_state + max_tiles);
+    P.max_tiles = max_tiles;
+    CUDA_TRY(cudaMemsetAsync(P.tile_state, 0, (size_t)(max_tiles + 1) * 8, stream));
+    static bool attr_set = false;
+    if (!attr_set) {
+        CUDA_TRY(cudaFuncSetAttribute(stream_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileShared)));
+        attr_set = true;
+    }
+    int64_t grid = 2 * (int64_t)sm_count();
+    if (grid > max_tiles) grid = max_tiles;
+    stream_tile_kernel<<<(unsigned)grid, kTileThreads, sizeof(TileShared), stream>>>(P);
     LAUNCHED();
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
@@ -459,10 +540,10 @@ int qb200_stream_feed_batch_noalloc(const qb200_tags* tags, const uint8_t* chunk
     void* scratch = nullptr;
     int rc = noalloc_scratch_ptr(&scratch);
     if (rc != QB200_OK) return rc;
-    // same kernels, same order as the allocating-caller entry point; only the scratch comes from the static array
-    return qb200_stream_feed_batch(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, state_in, state_out, flags,
-                                   out_bytes, out_capacity, out_chunk_off, scratch, (size_t)QB200_NOALLOC_SCRATCH_BYTES_,
-                                   stream_);
+    // the general three-kernel path (count, scan, copy) with its scratch taken from the static array
+    return stream_feed_general(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, state_in, state_out, flags,
+                               out_bytes, out_capacity, out_chunk_off, scratch, (size_t)QB200_NOALLOC_SCRATCH_BYTES_,
+                               (cudaStream_t)stream_);
 }
 
 int qb200_stream_flush_batch(qb200_stream_state* state, int64_t n_streams, void* stream_) {

@@ -22,6 +22,10 @@ struct DevTags {
     uint8_t len[kMaxTags];
     uint8_t cls_base[kMaxTags];
     uint8_t name[kMaxTags][kNameStride];
+    // fast matcher (ASCII spellings): the 24 bytes after "<" or "</" are compared as six 32-bit words against
+    // name + '>' :  ((text | om) & lm) == pk.   om = 0x20 at letter positions, lm = 0xFF over the pattern length.
+    uint32_t pk[kMaxTags][6], om[kMaxTags][6], lm[kMaxTags][6];
+    uint32_t first_ok[8];  // bytes that may follow '<' in a tag ('/', first letters in both cases, fold lead bytes, '>' for "")
 };
 
 struct StreamState {  // == qb200_stream_state
@@ -118,6 +122,60 @@ __device__ int64_t match_tag(const DevTags& tg, const A& B, int64_t x, int64_t e
         }
     }
     return -1;
+}
+
+// Fast tag recognition on a shared-memory copy (at least 36 readable bytes after x).  Same result as match_tag for
+// open and close tags together: returns the tag length in bytes (0 = not a tag); is_close, cls, exrel (offset of the
+// first U+0130/U+0131/U+017F form, 0xFF if none) as in match_tag.  ASCII spellings take the word-compare path; anything
+// with a non-ASCII byte in the window falls back to the exact byte-wise matcher.
+__device__ __forceinline__ int fast_match_tag(const DevTags& tg, const uint8_t* D, int x, int end, int& is_close, int& cls,
+                                              int& exrel) {
+    is_close = 0;
+    cls = 0;
+    exrel = 0xFF;
+    if (x + 1 >= end) return 0;
+    const uint8_t c1 = D[x + 1];
+    if (!((tg.first_ok[c1 >> 5] >> (c1 & 31)) & 1u)) return 0;
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(D + ((x + 1) & ~3));
+    const int sh = ((x + 1) & 3) * 8;
+    uint32_t r0 = w[0], r1 = w[1], r2 = w[2], r3 = w[3], r4 = w[4], r5 = w[5], r6 = w[6], r7 = w[7];
+    uint32_t b0 = __funnelshift_r(r0, r1, sh), b1 = __funnelshift_r(r1, r2, sh), b2 = __funnelshift_r(r2, r3, sh),
+             b3 = __funnelshift_r(r3, r4, sh), b4 = __funnelshift_r(r4, r5, sh), b5 = __funnelshift_r(r5, r6, sh),
+             b6 = __funnelshift_r(r6, r7, sh);
+    if ((b0 & 0xffu) == '/') {
+        is_close = 1;
+        b0 = __funnelshift_r(b0, b1, 8);
+        b1 = __funnelshift_r(b1, b2, 8);
+        b2 = __funnelshift_r(b2, b3, 8);
+        b3 = __funnelshift_r(b3, b4, 8);
+        b4 = __funnelshift_r(b4, b5, 8);
+        b5 = __funnelshift_r(b5, b6, 8);
+    }
+    const int avail = end - x - 1 - is_close;  // bytes available for name + '>'
+    for (int i = 0; i < tg.n; i++) {
+        if (((b0 | tg.om[i][0]) & tg.lm[i][0]) != tg.pk[i][0]) continue;
+        const int L = tg.len[i] + 1;
+        if (L > avail) continue;
+        if (L > 4) {
+            uint32_t d = (((b1 | tg.om[i][1]) & tg.lm[i][1]) ^ tg.pk[i][1]) | (((b2 | tg.om[i][2]) & tg.lm[i][2]) ^ tg.pk[i][2]);
+            if (L > 12)
+                d |= (((b3 | tg.om[i][3]) & tg.lm[i][3]) ^ tg.pk[i][3]) | (((b4 | tg.om[i][4]) & tg.lm[i][4]) ^ tg.pk[i][4]) |
+                     (((b5 | tg.om[i][5]) & tg.lm[i][5]) ^ tg.pk[i][5]);
+            if (d) continue;
+        }
+        cls = tg.cls_base[i];
+        return 1 + is_close + L;
+    }
+    if ((b0 | b1 | b2 | b3 | b4 | b5) & 0x80808080u) {  // possible U+0130/0131/212A/017F spelling: exact matcher
+        const PtrAcc A{D};
+        int64_t ex;
+        int64_t tend = match_tag(tg, A, x, end, is_close != 0, cls, ex);
+        if (tend >= 0) {
+            if (ex >= 0) exrel = (int)(ex - x);
+            return (int)(tend - x);
+        }
+    }
+    return 0;
 }
 
 // Text [x, end) starts with '<' and is not a complete tag: is it a byte prefix of some complete tag?

@@ -1,13 +1,14 @@
 // Fused single-pass tile kernels: every input byte is read from HBM once (TMA bulk copy into shared memory), every output
 // byte is written once, output offsets come from a decoupled look-back over tiles.
 //
-// Work assignment: the flat input is cut into 32 KiB windows; tile t owns the units (streams / responses) whose first
-// byte lies in window t, so units are never split and a tile's bytes are contiguous.  A CTA takes tiles from a ticket
-// counter (tiles start in index order, which the look-back needs for forward progress).
+// Work assignment: the flat input is cut into 16 KiB windows; tile t owns the units (streams / responses) whose first
+// byte lies in window t, so units are never split and a tile's bytes are contiguous (a small pre-pass kernel writes
+// every tile's unit / byte / chunk range).  A CTA takes tiles from a ticket counter (tiles start in index order, which
+// the look-back needs for forward progress).
 //
 // Inside a tile (fast path, everything in shared memory):
 //   A  all warps, one 1 KiB step each: '<' bitmap (16-byte shared loads + SWAR), tag matching at the candidates
-//      against the tag table -> ordered token list (ballot/popc ranks + block scan of per-step counts)
+//      against the tag table -> token records in per-step slots (popc ranks by warp scan)
 //   B  one warp per unit: sequential automaton over the (sparse) token list -> kept segments, kept bitmap painted
 //   C  block scan of kept-byte counts per word; one thread per feed boundary: release boundary + hold-back test
 //   D  block scan of per-unit output lengths, tile aggregate, decoupled look-back -> tile output base
@@ -19,17 +20,18 @@
 
 namespace qb {
 
-constexpr int kWindow = 32768;            // bytes of input per tile window
-constexpr int kStageCap = 65536 + 64;     // staged bytes per tile: any unit <= 32 KiB that starts in the window fits
-constexpr int kTileWarps = 16;
+constexpr int kWindow = 16384;            // bytes of input per tile window
+constexpr int kStageCap = 32768 + 64;     // staged bytes per tile: a unit <= 16 KiB starting anywhere in the window fits,
+                                          // a 32 KiB unit fits when it starts at the window start
+constexpr int kTileWarps = 8;
 constexpr int kTileThreads = kTileWarps * 32;
 constexpr int kMaxSteps = (kStageCap + 1023) / 1024;
 constexpr int kStageWords = kMaxSteps * 32;
 constexpr int kMaxUnits = 64;
-constexpr int kTokCap = 640;
-constexpr int kSegCap = 320;
-constexpr int kChunkCap = 1088;
-constexpr int kSegPiece = 2048;           // long kept runs are split so the copy spreads over warps
+constexpr int kSlots = 8;                 // token slots per 1 KiB step
+constexpr int kSegCap = 192;
+constexpr int kChunkCap = 576;
+constexpr int kSegPiece = 1024;           // long kept runs are split so the copy spreads over warps
 
 // ---------------------------------------------------------------------------------------------------------------
 // PTX helpers: mbarrier + TMA bulk copy (cp.async.bulk -> UBLKCP)
@@ -86,7 +88,10 @@ __device__ inline int64_t lookback_exclusive(unsigned long long* tile_state, int
         const unsigned inval = __ballot_sync(kFull, st == 0);
         const int firstp = has_p ? __ffs(has_p) - 1 : 32;
         const unsigned need = firstp >= 31 ? 0xffffffffu : ((2u << firstp) - 1u);
-        if (inval & need) continue;  // a predecessor has not published yet: poll again
+        if (inval & need) {  // a predecessor has not published yet: poll again, without hogging the issue slots
+            __nanosleep(40);
+            continue;
+        }
         int64_t val = (lane <= firstp) ? (int64_t)(v & kStMask) : 0;
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(kFull, val, d);
@@ -98,51 +103,6 @@ __device__ inline int64_t lookback_exclusive(unsigned long long* tile_state, int
     return excl;
 }
 
-// Warp-cooperative lower bound: smallest u in [0, n] with start(u) >= key (start non-decreasing, start(n) = total).
-// `guess` narrows the first round when units are uniform.
-template <class F>
-__device__ inline int64_t warp_lower_bound(F start, int64_t n, int64_t key, int64_t guess, int lane) {
-    int64_t lo = 0, hi = n;
-    {   // probe 32 consecutive units around the guess
-        int64_t g0 = guess - 15;
-        if (g0 < 0) g0 = 0;
-        if (g0 > n) g0 = n;
-        const int64_t idx = g0 + lane;
-        const bool ge = idx >= n ? true : (start(idx) >= key);
-        const unsigned b = __ballot_sync(kFull, ge);
-        if (b == 0) {
-            lo = g0 + 32;
-        } else {
-            const int f = __ffs(b) - 1;
-            if (f > 0) return g0 + f;  // start(g0+f-1) < key <= start(g0+f)
-            hi = g0;                   // start(g0) >= key
-        }
-        if (lo > hi) lo = hi;
-    }
-    while (lo < hi) {
-        const int64_t span = hi - lo;
-        const int64_t step = (span + 31) / 32;
-        const int64_t idx = lo + (int64_t)lane * step;
-        const bool ge = idx >= hi ? true : (start(idx) >= key);
-        const unsigned b = __ballot_sync(kFull, ge);
-        if (b == 0) {  // every probe is below the key
-            lo = lo + 31 * step + 1;
-            continue;
-        }
-        const int f = __ffs(b) - 1;
-        if (f == 0) {
-            hi = lo;
-        } else {
-            const int64_t nlo = lo + (int64_t)(f - 1) * step + 1;
-            int64_t nhi = lo + (int64_t)f * step;
-            if (nhi > hi) nhi = hi;
-            lo = nlo;
-            hi = nhi;
-        }
-    }
-    return lo;
-}
-
 // token record: x = tile-relative position of '<';  y = len | close<<8 | cls<<9 | exrel<<16 (0xFF = no exotic form)
 struct Tok {
     uint32_t x, y;
@@ -152,29 +112,33 @@ struct Seg {
     uint32_t src, len, dst;
     uint16_t unit, final_;
 };
+// Written by the pre-pass: the units / bytes / items (chunks or requests) a tile owns.  u0p1 == 0: no unit starts here.
+struct TileRec {
+    int64_t u0p1, u1, b0, b1, c0, c1;
+};
 
 struct TileShared {
     uint64_t mbar;
-    // tile geometry (written by warp 0)
-    int64_t g0;        // absolute offset of the first staged byte (multiple of 32)
-    int64_t u0, u1;    // unit range of this tile
-    int64_t c0;        // (streams) absolute index of the tile's first chunk
-    int64_t tile_base; // output offset of the tile
-    int32_t staged;    // staged bytes
+    int64_t g0;         // absolute offset of the first staged byte (multiple of 32)
+    int64_t u0, u1;     // unit range of this tile
+    int64_t c0;         // (streams) absolute index of the tile's first chunk
+    int64_t tile_base;  // output offset of the tile
+    unsigned long long agg;  // general path: sum of unit totals
+    int32_t staged;     // staged bytes
     int32_t nunits, nchunks, nsteps;
-    int32_t fast;      // 1 = fast path
-    int32_t ntok, nseg;
+    int32_t fast;       // 1 = fast path
+    int32_t nseg;
     int32_t overflow;
-    unsigned long long agg;  // fallback: sum of unit totals
     int32_t tile;
-    int32_t step_tok[kMaxSteps + 2];   // tokens per step -> exclusive offsets
+    int32_t tile_total;
+    int32_t step_tok[kMaxSteps + 2];   // tokens recorded per step
     int32_t step_cum[kMaxSteps + 2];   // kept bytes before the step
-    int32_t u_beg[kMaxUnits + 1], u_end[kMaxUnits + 1];       // tile-relative byte range
+    int32_t u_beg[kMaxUnits + 1], u_end[kMaxUnits + 1];  // tile-relative byte range
     int32_t u_cend[kMaxUnits + 1];     // cumulative chunk count up to and including the unit (tile-local)
     int32_t u_depth[kMaxUnits], u_last_tok_end[kMaxUnits], u_total[kMaxUnits], u_out_rel[kMaxUnits + 1];
-    int32_t u_rlast[kMaxUnits], u_gbeg[kMaxUnits];
+    int32_t u_rlast[kMaxUnits];
     uint8_t u_held_kept[kMaxUnits], u_held_unc[kMaxUnits];
-    Tok tok[kTokCap];
+    Tok tok[kMaxSteps * kSlots];
     Seg seg[kSegCap];
     int32_t bnd[kChunkCap];            // feed boundaries: tile-relative position, later (unit<<24 | released bytes before)
     uint32_t ltbm[kStageWords];        // '<' bitmap, one word per 32 bytes
@@ -183,32 +147,49 @@ struct TileShared {
     __align__(128) uint8_t data[kStageCap + 64];
 };
 
-// block-wide exclusive scan of one int per thread (kTileThreads threads); returns exclusive value, total via out param
-__device__ inline int block_excl_scan(int v, int* warp_tmp /* kTileWarps+1 ints in shared */, int& total) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    int incl = v;
+// exclusive scan of a[0..n), n <= 64, by one full warp; returns the total
+__device__ inline int warp_scan64(int32_t* a, int n, int lane) {
+    const int v0 = lane < n ? a[lane] : 0, v1 = lane + 32 < n ? a[lane + 32] : 0;
+    int i0 = v0, i1 = v1;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-        int t = __shfl_up_sync(kFull, incl, d);
-        if (lane >= d) incl += t;
-    }
-    if (lane == 31) warp_tmp[wid] = incl;
-    __syncthreads();
-    if (wid == 0) {
-        int ws = lane < kTileWarps ? warp_tmp[lane] : 0, wi = ws;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int t = __shfl_up_sync(kFull, wi, d);
-            if (lane >= d) wi += t;
+        int t0 = __shfl_up_sync(kFull, i0, d), t1 = __shfl_up_sync(kFull, i1, d);
+        if (lane >= d) {
+            i0 += t0;
+            i1 += t1;
         }
-        if (lane < kTileWarps) warp_tmp[lane] = wi - ws;
-        if (lane == 31) warp_tmp[kTileWarps] = wi;
     }
-    __syncthreads();
-    const int r = warp_tmp[wid] + incl - v;
-    total = warp_tmp[kTileWarps];
-    __syncthreads();
-    return r;
+    const int tot0 = __shfl_sync(kFull, i0, 31), tot1 = __shfl_sync(kFull, i1, 31);
+    if (lane < n) a[lane] = i0 - v0;
+    if (lane + 32 < n) a[lane + 32] = tot0 + i1 - v1;
+    return tot0 + tot1;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// pre-pass: which units does every 16 KiB window own?  One thread per unit; exactly one writer per field.
+// ---------------------------------------------------------------------------------------------------------------
+// streams: unit start = chunk_off[stream_off[u]], item index = chunk index
+__global__ void stream_tile_map_kernel(const int64_t* __restrict__ chunk_off, int64_t n_chunks,
+                                       const int64_t* __restrict__ stream_off, int64_t n_streams, TileRec* __restrict__ rec,
+                                       int64_t max_tiles) {
+    const int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= n_streams) return;
+    const int64_t c = stream_off[u], cn = stream_off[u + 1];
+    const int64_t b = chunk_off[c], bn = chunk_off[cn];
+    const int64_t t = b / kWindow;
+    if (t >= max_tiles) return;
+    const int64_t tp = u > 0 ? chunk_off[stream_off[u - 1]] / kWindow : -1;
+    const int64_t tn = u + 1 < n_streams ? bn / kWindow : -2;
+    if (tp != t) {
+        rec[t].u0p1 = u + 1;
+        rec[t].b0 = b;
+        rec[t].c0 = c;
+    }
+    if (tn != t) {
+        rec[t].u1 = u + 1;
+        rec[t].b1 = bn;
+        rec[t].c1 = cn;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -226,17 +207,76 @@ struct StreamTileParams {
     uint32_t flags;
     uint8_t* out;
     int64_t* out_chunk_off;
-    unsigned long long* tile_state;  // [n_tiles], zeroed
+    unsigned long long* tile_state;  // [max_tiles], zeroed
+    const TileRec* rec;              // [max_tiles], zeroed then filled by the pre-pass
     unsigned int* ticket;            // zeroed
-    int64_t* unit_totals;            // [n_streams] scratch (fallback path)
-    int64_t* unit_bases;             // [n_streams] scratch (fallback path)
+    int64_t* unit_totals;            // [n_streams] scratch (general path)
+    int64_t* unit_bases;             // [n_streams] scratch (general path)
     int64_t max_tiles;               // tiles the scratch has room for (>= total / kWindow + 1)
 };
 
-__global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __grid_constant__ StreamTileParams P) {
+// General path inside a tile: warp-per-unit walkers (qb_walk.cuh), reading a unit from shared memory when it was staged
+// and from global memory otherwise; per-unit results go through global scratch because the unit count is unbounded.
+__device__ __noinline__ void stream_tile_general(const StreamTileParams& P, TileShared& S, int64_t tile, int64_t g0,
+                                                 int staged, int64_t total) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const DevTags& tg = P.tg;
+    const int64_t u0 = S.u0, u1 = S.u1;
+    const uint8_t* sbuf = S.data - g0;  // sbuf + absolute offset addresses the staged copy
+    for (int64_t s = u0 + wid; s < u1; s += kTileWarps) {
+        const int64_t cf = P.stream_off[s], m = P.stream_off[s + 1] - cf;
+        const int64_t ue = P.chunk_off[cf + m];
+        const bool in_smem = ue - g0 <= staged;
+        StreamWalker<false> w(tg, in_smem ? sbuf : P.bytes, in_smem ? g0 + staged : total, P.chunk_off + cf, m, lane, P.flags);
+        StreamResult r = w.run(P.st_in ? P.st_in + s : nullptr, nullptr);
+        if (lane == 0) {
+            P.unit_totals[s] = r.total_out;
+            atomicAdd(&S.agg, (unsigned long long)r.total_out);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    if (wid == 0) {
+        int64_t base = lookback_exclusive(P.tile_state, tile, (int64_t)S.agg, lane);
+        if (lane == 0) S.tile_base = base;
+    }
+    if (wid == 1 % kTileWarps) {  // exclusive offsets of the tile's units
+        int64_t run = 0;
+        for (int64_t b = u0; b < u1; b += 32) {
+            const int64_t s = b + lane;
+            const int64_t v = s < u1 ? P.unit_totals[s] : 0;
+            int64_t incl = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int64_t t = __shfl_up_sync(kFull, incl, d);
+                if (lane >= d) incl += t;
+            }
+            if (s < u1) P.unit_bases[s] = run + incl - v;
+            run += __shfl_sync(kFull, incl, 31);
+        }
+    }
+    __syncthreads();
+    const int64_t tbase = S.tile_base;
+    if (tile == 0 && tid == 0) P.out_chunk_off[0] = 0;
+    for (int64_t s = u0 + wid; s < u1; s += kTileWarps) {
+        const int64_t cf = P.stream_off[s], m = P.stream_off[s + 1] - cf;
+        const int64_t ue = P.chunk_off[cf + m];
+        const bool in_smem = ue - g0 <= staged;
+        StreamWalker<true> w(tg, in_smem ? sbuf : P.bytes, in_smem ? g0 + staged : total, P.chunk_off + cf, m, lane, P.flags);
+        w.out_base = tbase + P.unit_bases[s];
+        w.dst = P.out + w.out_base;
+        w.out_chunk_off = P.out_chunk_off;
+        w.chunk0 = cf;
+        StreamState si;
+        if (P.st_in) si = P.st_in[s];
+        w.run(P.st_in ? &si : nullptr, P.st_out ? P.st_out + s : nullptr);
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __grid_constant__ StreamTileParams P) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     TileShared& S = *reinterpret_cast<TileShared*>(smem_raw);
-    __shared__ int scan_tmp[kTileWarps + 1];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const DevTags& tg = P.tg;
     const int64_t total = P.chunk_off[P.n_chunks];
@@ -245,61 +285,44 @@ __global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __gr
     if (tid == 0) mbar_init(&S.mbar, 1);
     __syncthreads();
 
-    auto ustart = [&](int64_t s) -> int64_t { return s >= P.n_streams ? total : P.chunk_off[P.stream_off[s]]; };
-
     for (;;) {
         // ---- take a tile ----
         __syncthreads();
-        if (tid == 0) S.tile = (int32_t)atomicAdd(P.ticket, 1u);
-        __syncthreads();
-        const int64_t tile = S.tile;
-        if (tile >= n_tiles) break;
-
-        if (wid == 0) {
-            const int64_t w0 = tile * (int64_t)kWindow, w1 = w0 + kWindow;
-            const int64_t guess0 = total > 0 ? (int64_t)((double)w0 / (double)total * (double)P.n_streams) : 0;
-            const int64_t u0 = warp_lower_bound(ustart, P.n_streams, w0, guess0, lane);
-            const int64_t step_guess = P.n_streams > 0 && total > 0 ? (int64_t)((double)kWindow / ((double)total / (double)P.n_streams)) : 0;
-            int64_t u1 = (tile == n_tiles - 1) ? P.n_streams : warp_lower_bound(ustart, P.n_streams, w1, u0 + step_guess, lane);
-            if (u1 < u0) u1 = u0;
-            const int64_t b0 = ustart(u0), b1 = ustart(u1);
-            const int64_t g0 = b0 & ~(int64_t)31;
-            const int64_t nun = u1 - u0;
-            const int64_t c0 = u0 < P.n_streams ? P.stream_off[u0] : P.n_chunks;
-            const int64_t c1 = u1 < P.n_streams ? P.stream_off[u1] : P.n_chunks;
-            const bool fits = (b1 - g0) <= kStageCap;
-            if (lane == 0) {
+        if (tid == 0) {
+            const int64_t tile = (int64_t)atomicAdd(P.ticket, 1u);
+            S.tile = (int32_t)tile;
+            if (tile < n_tiles) {
+                const TileRec r = P.rec[tile];
+                const int64_t nun = r.u0p1 ? r.u1 - (r.u0p1 - 1) : 0;
+                const int64_t g0 = r.b0 & ~(int64_t)31;
+                const bool fits = (r.b1 - g0) <= kStageCap;
                 S.g0 = g0;
-                S.u0 = u0;
-                S.u1 = u1;
-                S.c0 = c0;
+                S.u0 = r.u0p1 - 1;
+                S.u1 = r.u1;
+                S.c0 = r.c0;
                 S.nunits = (int32_t)(nun > 0x7fffffff ? 0x7fffffff : nun);
-                S.nchunks = (int32_t)((c1 - c0) > 0x7fffffff ? 0x7fffffff : (c1 - c0));
-                int64_t stg = fits ? (b1 - g0) : kStageCap;
+                S.nchunks = (int32_t)((r.c1 - r.c0) > 0x7fffffff ? 0x7fffffff : (r.c1 - r.c0));
+                int64_t stg = fits ? (r.b1 - g0) : kStageCap;
                 if (g0 + stg > total) stg = total - g0;
+                if (nun == 0) stg = 0;
                 S.staged = (int32_t)stg;
                 S.nsteps = (int32_t)((stg + 1023) >> 10);
-                S.fast = (fits && nun <= kMaxUnits && nun > 0 && (c1 - c0) <= kChunkCap) ? 1 : 0;
-                S.ntok = 0;
+                S.fast = (fits && nun <= kMaxUnits && nun > 0 && (r.c1 - r.c0) <= kChunkCap) ? 1 : 0;
                 S.nseg = 0;
                 S.overflow = 0;
                 S.agg = 0;
                 // stage [g0, g0 + staged): TMA bulk copy of the 16-byte multiple, tail bytes by hand below
                 const uint32_t bulk = (uint32_t)(stg & ~(int64_t)15);
-                if (nun > 0 && bulk > 0) {
+                if (bulk > 0) {
                     fence_proxy_async();
                     mbar_expect_tx(&S.mbar, bulk);
-                    uint32_t done = 0;
-                    while (done < bulk) {
-                        uint32_t n = bulk - done;
-                        if (n > 32768u) n = 32768u;
-                        bulk_g2s(S.data + done, P.bytes + g0 + done, n, &S.mbar);
-                        done += n;
-                    }
+                    bulk_g2s(S.data, P.bytes + g0, bulk, &S.mbar);
                 }
             }
         }
         __syncthreads();
+        const int64_t tile = S.tile;
+        if (tile >= n_tiles) break;
         const int nunits = S.nunits;
         if (nunits == 0) {
             if (tile == 0 && tid == 0) P.out_chunk_off[0] = 0;
@@ -313,129 +336,96 @@ __global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __gr
         if (fast) {
             for (int u = tid; u <= nunits; u += kTileThreads) {
                 const int64_t s = S.u0 + u;
-                const int64_t b = ustart(s);
-                const int64_t ce = (s < P.n_streams ? P.stream_off[s] : P.n_chunks) - S.c0;
-                if (u < nunits) S.u_beg[u] = (int32_t)(b - g0);
+                const int64_t cs = s < P.n_streams ? P.stream_off[s] : P.n_chunks;
+                const int64_t b = P.chunk_off[cs];
+                if (u < nunits) {
+                    S.u_beg[u] = (int32_t)(b - g0);
+                    S.u_rlast[u] = 0;
+                    S.u_total[u] = 0;
+                }
                 if (u > 0) {
                     S.u_end[u - 1] = (int32_t)(b - g0);
-                    S.u_cend[u - 1] = (int32_t)ce;
+                    S.u_cend[u - 1] = (int32_t)(cs - S.c0);
                 }
             }
             for (int i = tid; i < S.nchunks; i += kTileThreads) S.bnd[i] = (int32_t)(P.chunk_off[S.c0 + 1 + i] - g0);
             for (int i = tid; i < kStageWords; i += kTileThreads) S.keptbm[i] = 0;
         }
-        // tail bytes the bulk copy could not take (size not a multiple of 16)
-        {
+        {   // tail bytes the bulk copy could not take (size not a multiple of 16), then wait for the copy
             const int bulk = staged & ~15;
             if (tid < staged - bulk) S.data[bulk + tid] = P.bytes[g0 + bulk + tid];
-            if ((staged & ~15) > 0) {
+            if (bulk > 0) {
                 while (!mbar_try_wait(&S.mbar, parity)) {}
+                parity ^= 1;
             }
         }
-        if ((staged & ~15) > 0) parity ^= 1;
         __syncthreads();
 
         if (fast) {
             const int nsteps = S.nsteps;
             const int lo_pos = S.u_beg[0], hi_pos = S.u_end[nunits - 1];
-            const PtrAcc D{S.data};
-            // unit containing tile-relative position x
-            auto unit_of = [&](int x) -> int {
+            auto unit_end_of = [&](int x) -> int {  // end of the unit containing tile-relative position x
                 int lo = 0, hi = nunits - 1;
                 while (lo < hi) {
                     int mid = (lo + hi) >> 1;
                     if (S.u_end[mid] > x) hi = mid;
                     else lo = mid + 1;
                 }
-                return lo;
+                return S.u_end[lo];
             };
-            // ---- A: '<' bitmap and token masks, one step per warp at a time ----
-            uint32_t tokm[(kMaxSteps + kTileWarps - 1) / kTileWarps];
-#pragma unroll
-            for (int k = 0; k < (kMaxSteps + kTileWarps - 1) / kTileWarps; k++) {
-                tokm[k] = 0;
-                const int st = wid + k * kTileWarps;
-                if (st < nsteps) {
-                    const int wi = st * 32 + lane;
-                    const int wb = wi * 32;
+            // ---- A: '<' bitmap + token records, one 1 KiB step per warp at a time ----
+            for (int st = wid; st < nsteps; st += kTileWarps) {
+                const int wi = st * 32 + lane;
+                const int wb = wi * 32;
+                uint32_t lt = 0;
+                if (wb < staged) {
                     const uint4* p = reinterpret_cast<const uint4*>(S.data + wb);
-                    uint32_t lt = 0;
-                    if (wb < staged) {
-                        uint4 a = p[0], b = p[1];
-                        lt = lt_mask16(a) | (lt_mask16(b) << 16);
-                        lt &= mask_ge(wb, lo_pos) & ~mask_ge(wb, hi_pos);
-                    }
-                    S.ltbm[wi] = lt;
-                    uint32_t mm = lt, tk = 0;
-                    while (mm) {
-                        const int b = __ffs(mm) - 1;
-                        mm &= mm - 1;
-                        const int x = wb + b;
-                        const int ue = S.u_end[unit_of(x)];
-                        int cls;
-                        int64_t ex;
-                        if (match_tag(tg, D, x, ue, false, cls, ex) >= 0 || match_tag(tg, D, x, ue, true, cls, ex) >= 0)
-                            tk |= 1u << b;
-                    }
-                    tokm[k] = tk;
-                    int cnt = __popc(tk);
-#pragma unroll
-                    for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(kFull, cnt, d);
-                    if (lane == 0) S.step_tok[st] = cnt;
+                    uint4 a = p[0], b = p[1];
+                    lt = lt_mask16(a) | (lt_mask16(b) << 16);
+                    lt &= mask_ge(wb, lo_pos) & ~mask_ge(wb, hi_pos);
                 }
-            }
-            __syncthreads();
-            {   // exclusive offsets of the steps' tokens
-                int v = tid < nsteps ? S.step_tok[tid] : 0, tot;
-                int e = block_excl_scan(v, scan_tmp, tot);
-                if (tid < nsteps) S.step_tok[tid] = e;
-                if (tid == 0) {
-                    S.ntok = tot;
-                    if (tot > kTokCap) S.overflow = 1;
-                }
-            }
-            __syncthreads();
-            if (!S.overflow) {
-#pragma unroll
-                for (int k = 0; k < (kMaxSteps + kTileWarps - 1) / kTileWarps; k++) {
-                    const int st = wid + k * kTileWarps;
-                    if (st < nsteps) {
-                        uint32_t tk = tokm[k];
-                        int pc = __popc(tk), incl = pc;
-#pragma unroll
-                        for (int d = 1; d < 32; d <<= 1) {
-                            int t = __shfl_up_sync(kFull, incl, d);
-                            if (lane >= d) incl += t;
-                        }
-                        int slot = S.step_tok[st] + incl - pc;
-                        const int wb = (st * 32 + lane) * 32;
-                        while (tk) {
-                            const int b = __ffs(tk) - 1;
-                            tk &= tk - 1;
-                            const int x = wb + b;
-                            const int ue = S.u_end[unit_of(x)];
-                            int cls;
-                            int64_t ex;
-                            int is_close = 0;
-                            int64_t tend = match_tag(tg, D, x, ue, false, cls, ex);
-                            if (tend < 0) {
-                                tend = match_tag(tg, D, x, ue, true, cls, ex);
-                                is_close = 1;
-                            }
-                            Tok t;
-                            t.x = (uint32_t)x;
-                            t.y = (uint32_t)(tend - x) | (is_close << 8) | (cls << 9) | ((ex >= 0 ? (uint32_t)(ex - x) : 0xFFu) << 16);
-                            S.tok[slot++] = t;
-                        }
+                S.ltbm[wi] = lt;
+                Tok r0{0, 0}, r1{0, 0};
+                int cnt = 0;
+                bool many = false;
+                while (lt) {
+                    const int b = __ffs(lt) - 1;
+                    lt &= lt - 1;
+                    const int x = wb + b;
+                    int is_close, cls, exrel;
+                    const int len = fast_match_tag(tg, S.data, x, nunits == 1 ? hi_pos : unit_end_of(x), is_close, cls, exrel);
+                    if (len) {
+                        Tok t;
+                        t.x = (uint32_t)x;
+                        t.y = (uint32_t)len | (is_close << 8) | (cls << 9) | ((uint32_t)exrel << 16);
+                        if (cnt == 0) r0 = t;
+                        else if (cnt == 1) r1 = t;
+                        else many = true;
+                        cnt++;
                     }
                 }
+                int incl = cnt;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    int t = __shfl_up_sync(kFull, incl, d);
+                    if (lane >= d) incl += t;
+                }
+                const int tot = __shfl_sync(kFull, incl, 31);
+                const bool bad = __any_sync(kFull, many) || tot > kSlots;
+                if (bad) {
+                    if (lane == 0) S.overflow = 1;
+                } else {
+                    const int slot = st * kSlots + incl - cnt;
+                    if (cnt > 0) S.tok[slot] = r0;
+                    if (cnt > 1) S.tok[slot + 1] = r1;
+                }
+                if (lane == 0) S.step_tok[st] = bad ? 0 : tot;
             }
             __syncthreads();
         }
         const bool fastok = fast && !S.overflow;
 
         if (fastok) {
-            const int ntok = S.ntok;
             // ---- B: one warp per unit walks its tokens (all lanes in lock step, state uniform) ----
             for (int u = wid; u < nunits; u += kTileWarps) {
                 const int ub = S.u_beg[u], ue = S.u_end[u];
@@ -474,15 +464,13 @@ __global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __gr
                 };
                 auto emit = [&](int sa, int sb, int fin) {  // kept run [sa, sb) in unit coordinates
                     if (sb <= sa) return;
-                    // paint the kept bitmap
                     const int a = ub + sa, b = ub + sb;
                     const int w0 = a >> 5, w1 = (b - 1) >> 5;
-                    for (int w = w0 + lane; w <= w1; w += 32) {
+                    for (int w = w0 + lane; w <= w1; w += 32) {  // paint the kept bitmap
                         uint32_t msk = mask_ge(w * 32, a) & ~mask_ge(w * 32, b);
                         if (msk == 0xffffffffu) S.keptbm[w] = msk;
                         else atomicOr(&S.keptbm[w], msk);
                     }
-                    // segment records, split into pieces
                     const int len = sb - sa;
                     const int npieces = (len + kSegPiece - 1) / kSegPiece;
                     int slot = 0;
@@ -522,40 +510,29 @@ __global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __gr
                         }
                     }
                     cum = held_kept;
-                    // tokens of this unit: [t0, t1)
-                    int t0, t1;
-                    {
-                        int lo = 0, hi = ntok;
-                        while (lo < hi) {
-                            int mid = (lo + hi) >> 1;
-                            if ((int)S.tok[mid].x >= ub) hi = mid;
-                            else lo = mid + 1;
-                        }
-                        t0 = lo;
-                        hi = ntok;
-                        while (lo < hi) {
-                            int mid = (lo + hi) >> 1;
-                            if ((int)S.tok[mid].x >= ue) hi = mid;
-                            else lo = mid + 1;
-                        }
-                        t1 = lo;
-                    }
-                    for (int t = t0; t < t1; t++) {
-                        const Tok tk = S.tok[t];
-                        const int x = (int)tk.x - ub;
-                        const int tend = x + (int)(tk.y & 0xff);
-                        const bool is_close = (tk.y >> 8) & 1;
-                        const int exr = (tk.y >> 16) & 0xff;
-                        const int64_t ex = exr == 0xff ? -1 : x + exr;
-                        if (recognised(is_close, x, tend, ex)) {
-                            if (depth == 0) {
-                                emit(seg_start, x, 0);
-                                depth = 1;
-                            } else {
-                                depth += is_close ? -1 : 1;
-                                if (depth == 0) seg_start = tend;
+                    if (n > 0) {
+                        const int st0 = ub >> 10, st1 = (ue - 1) >> 10;
+                        for (int st = st0; st <= st1; st++) {
+                            const int cnt = S.step_tok[st];
+                            for (int k = 0; k < cnt; k++) {
+                                const Tok tk = S.tok[st * kSlots + k];
+                                if ((int)tk.x < ub || (int)tk.x >= ue) continue;
+                                const int x = (int)tk.x - ub;
+                                const int tend = x + (int)(tk.y & 0xff);
+                                const bool is_close = (tk.y >> 8) & 1;
+                                const int exr = (tk.y >> 16) & 0xff;
+                                const int64_t ex = exr == 0xff ? -1 : x + exr;
+                                if (recognised(is_close, x, tend, ex)) {
+                                    if (depth == 0) {
+                                        emit(seg_start, x, 0);
+                                        depth = 1;
+                                    } else {
+                                        depth += is_close ? -1 : 1;
+                                        if (depth == 0) seg_start = tend;
+                                    }
+                                    last_tok_end = tend;
+                                }
                             }
-                            last_tok_end = tend;
                         }
                     }
                     if (depth == 0) emit(seg_start, n, 1);
@@ -587,11 +564,9 @@ __global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __gr
                 if (lane == 31) S.step_cum[st] = incl;
             }
             __syncthreads();
-            {
-                int v = tid < nsteps ? S.step_cum[tid] : 0, tot;
-                int e = block_excl_scan(v, scan_tmp, tot);
-                if (tid < nsteps) S.step_cum[tid] = e;
-                if (tid == 0) S.step_cum[nsteps] = tot;
+            if (wid == 0) {
+                const int tot = warp_scan64(S.step_cum, nsteps, lane);
+                if (lane == 0) S.step_cum[nsteps] = tot;
             }
             __syncthreads();
             auto G = [&](int x) -> int {  // kept bytes in tile positions [0, x)
@@ -599,17 +574,10 @@ __global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __gr
                 if ((w >> 5) >= nsteps) return S.step_cum[nsteps];
                 return S.step_cum[w >> 5] + S.wpre[w] + (b ? __popc(S.keptbm[w] & ((1u << b) - 1u)) : 0);
             };
-            for (int u = tid; u < nunits; u += kTileThreads) {
-                S.u_gbeg[u] = G(S.u_beg[u]);
-                S.u_rlast[u] = 0;
-                S.u_total[u] = 0;
-            }
-            __syncthreads();
             const int nb = S.nchunks;
             for (int i = tid; i < nb; i += kTileThreads) {
                 const int cpos = S.bnd[i];
-                // unit of boundary i: first unit with u_cend > i
-                int lo = 0, hi = nunits - 1;
+                int lo = 0, hi = nunits - 1;  // unit of boundary i: first unit with u_cend > i
                 while (lo < hi) {
                     int mid = (lo + hi) >> 1;
                     if (S.u_cend[mid] > i) hi = mid;
@@ -619,7 +587,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __gr
                 const int ub = S.u_beg[u];
                 const int c = cpos - ub;  // unit coordinates
                 const int hk = S.u_held_kept[u];
-                int Pv = hk + G(cpos) - S.u_gbeg[u], R = c;
+                int Pv = hk + G(cpos) - G(ub), R = c;
                 bool found_lt = false;
                 if (c > 0) {
                     const int w = (cpos - 1) >> 5;
@@ -665,14 +633,13 @@ __global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __gr
             }
             __syncthreads();
             // ---- D: unit output offsets inside the tile, tile aggregate, look-back ----
-            {
-                int v = tid < nunits ? S.u_total[tid] : 0, tot;
-                int e = block_excl_scan(v, scan_tmp, tot);
-                if (tid < nunits) S.u_out_rel[tid] = e;
-                if (wid == 0) {
-                    int64_t base = lookback_exclusive(P.tile_state, tile, tot, lane);
-                    if (lane == 0) S.tile_base = base;
-                }
+            if (wid == 0) {
+                if (lane < nunits) S.u_out_rel[lane] = S.u_total[lane];
+                if (lane + 32 < nunits) S.u_out_rel[lane + 32] = S.u_total[lane + 32];
+                __syncwarp();
+                const int tot = warp_scan64(S.u_out_rel, nunits, lane);
+                const int64_t base = lookback_exclusive(P.tile_state, tile, tot, lane);
+                if (lane == 0) S.tile_base = base;
             }
             __syncthreads();
             // ---- E: offsets, state, bytes ----
@@ -681,6 +648,18 @@ __global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __gr
             for (int i = tid; i < nb; i += kTileThreads) {
                 const int v = S.bnd[i];
                 P.out_chunk_off[S.c0 + 1 + i] = tbase + S.u_out_rel[v >> 24] + (v & 0xffffff);
+            }
+            const int nseg = S.nseg;
+            for (int i = wid; i < nseg; i += kTileWarps) {
+                const Seg sg = S.seg[i];
+                const int u = sg.unit;
+                int len = (int)sg.len;
+                if (sg.final_) {  // the unit's last kept run is clipped at the last release boundary
+                    const int lim = S.u_beg[u] + S.u_rlast[u] - (int)sg.src;
+                    if (lim < len) len = lim;
+                }
+                if (len > 0)
+                    warp_copy(P.out + tbase + S.u_out_rel[u] + sg.dst, S.data + sg.src, len, S.data + kStageCap + 64, lane);
             }
             for (int u = tid; u < nunits; u += kTileThreads) {
                 const int64_t s = S.u0 + u;
@@ -705,8 +684,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __gr
                 } else {
                     const HeldAcc A{S.data + ub, si.held, h};
                     const int depth = S.u_depth[u], lte = S.u_last_tok_end[u], rl = S.u_rlast[u];
-                    // carried literal bytes come first in the unit's output
-                    if (S.u_held_kept[u] && rl > -h) {
+                    if (S.u_held_kept[u] && rl > -h) {  // carried literal bytes come first in the unit's output
                         uint8_t* d = P.out + tbase + S.u_out_rel[u];
                         for (int k = 0; k < h; k++) d[k] = si.held[k];
                     }
@@ -736,76 +714,8 @@ __global__ void __launch_bounds__(kTileThreads, 2) stream_tile_kernel(const __gr
                 }
                 if (P.st_out) P.st_out[s] = so;
             }
-            const int nseg = S.nseg;
-            for (int i = wid; i < nseg; i += kTileWarps) {
-                const Seg sg = S.seg[i];
-                const int u = sg.unit;
-                int len = (int)sg.len;
-                if (sg.final_) {  // the unit's last kept run is clipped at the last release boundary
-                    const int lim = S.u_beg[u] + S.u_rlast[u] - (int)sg.src;
-                    if (lim < len) len = lim;
-                }
-                if (len > 0)
-                    warp_copy(P.out + tbase + S.u_out_rel[u] + sg.dst, S.data + sg.src, len, S.data + kStageCap + 64, lane);
-            }
         } else {
-            // ---- general path inside the tile: warp-per-unit walkers, from shared memory when the unit is staged ----
-            const int64_t u0 = S.u0, u1 = S.u1;
-            const uint8_t* sbuf = S.data - g0;  // so that sbuf + absolute offset addresses the staged copy
-            for (int64_t s = u0 + wid; s < u1; s += kTileWarps) {
-                const int64_t cf = P.stream_off[s], m = P.stream_off[s + 1] - cf;
-                const int64_t ua = P.chunk_off[cf], ub_ = P.chunk_off[cf + m];
-                const bool in_smem = ub_ - g0 <= staged;
-                StreamWalker<false> w(tg, in_smem ? sbuf : P.bytes, in_smem ? g0 + staged : total, P.chunk_off + cf, m, lane,
-                                      P.flags);
-                (void)ua;
-                StreamResult r = w.run(P.st_in ? P.st_in + s : nullptr, nullptr);
-                if (lane == 0) {
-                    P.unit_totals[s] = r.total_out;
-                    atomicAdd(&S.agg, (unsigned long long)r.total_out);
-                }
-                __syncwarp();
-            }
-            __syncthreads();
-            if (wid == 0) {
-                int64_t base = lookback_exclusive(P.tile_state, tile, (int64_t)S.agg, lane);
-                if (lane == 0) S.tile_base = base;
-            }
-            // exclusive offsets of the tile's units (kept in global scratch: the unit count is unbounded here)
-            if (wid == 1) {
-                int64_t run = 0;
-                for (int64_t b = u0; b < u1; b += 32) {
-                    const int64_t s = b + lane;
-                    const int64_t v = s < u1 ? P.unit_totals[s] : 0;
-                    int64_t incl = v;
-#pragma unroll
-                    for (int d = 1; d < 32; d <<= 1) {
-                        int64_t t = __shfl_up_sync(kFull, incl, d);
-                        if (lane >= d) incl += t;
-                    }
-                    if (s < u1) P.unit_bases[s] = run + incl - v;
-                    run += __shfl_sync(kFull, incl, 31);
-                }
-            }
-            __threadfence_block();
-            __syncthreads();
-            const int64_t tbase = S.tile_base;
-            if (tile == 0 && tid == 0) P.out_chunk_off[0] = 0;
-            for (int64_t s = u0 + wid; s < u1; s += kTileWarps) {
-                const int64_t cf = P.stream_off[s], m = P.stream_off[s + 1] - cf;
-                const int64_t ub_ = P.chunk_off[cf + m];
-                const bool in_smem = ub_ - g0 <= staged;
-                StreamWalker<true> w(tg, in_smem ? sbuf : P.bytes, in_smem ? g0 + staged : total, P.chunk_off + cf, m, lane,
-                                     P.flags);
-                w.out_base = tbase + P.unit_bases[s];
-                w.dst = P.out + w.out_base;
-                w.out_chunk_off = P.out_chunk_off;
-                w.chunk0 = cf;
-                StreamState si;
-                if (P.st_in) si = P.st_in[s];
-                w.run(P.st_in ? &si : nullptr, P.st_out ? P.st_out + s : nullptr);
-                __syncwarp();
-            }
+            stream_tile_general(P, S, tile, g0, staged, total);
         }
     }
 }

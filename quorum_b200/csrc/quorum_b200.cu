@@ -286,6 +286,35 @@ int qb200_tags_create(const uint8_t* names, const int32_t* name_off, int32_t n_t
         ncls = 1;
     }
     d.ncls = ncls;
+    // fast-matcher tables
+    auto set_ok = [&](unsigned c) { d.first_ok[c >> 5] |= 1u << (c & 31); };
+    set_ok('/');
+    for (int i = 0; i < d.n; i++) {
+        uint8_t pat[24], orm[24], lenm[24];
+        memset(pat, 0, 24);
+        memset(orm, 0, 24);
+        memset(lenm, 0, 24);
+        const int L = d.len[i];
+        for (int k = 0; k < L; k++) {
+            const uint8_t c = d.name[i][k];
+            pat[k] = c;
+            orm[k] = (c >= 'a' && c <= 'z') ? 0x20 : 0;
+            lenm[k] = 0xFF;
+        }
+        pat[L] = '>';
+        lenm[L] = 0xFF;
+        for (int k = 0; k < 6; k++) {
+            memcpy(&d.pk[i][k], pat + 4 * k, 4);
+            memcpy(&d.om[i][k], orm + 4 * k, 4);
+            memcpy(&d.lm[i][k], lenm + 4 * k, 4);
+        }
+        const uint8_t f = L ? d.name[i][0] : (uint8_t)'>';
+        set_ok(f);
+        if (f >= 'a' && f <= 'z') set_ok(f - 32);
+        if (f == 'i') set_ok(0xC4);
+        if (f == 'k') set_ok(0xE2);
+        if (f == 's') set_ok(0xC5);
+    }
     *out = t;
     return QB200_OK;
 }
@@ -372,9 +401,12 @@ static size_t stream_general_scratch_bytes(int64_t n_streams) {
 
 static int64_t tiles_for(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte_bound) / kWindow + 2; }
 
+// per tile: look-back state word + TileRec; plus the ticket
+static size_t tile_scratch_bytes(int64_t max_tiles) { return align256((size_t)max_tiles * (8 + sizeof(TileRec)) + 64); }
+
 size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity) {
     (void)n_chunks;
-    return stream_general_scratch_bytes(n_streams) + align256((size_t)(tiles_for(out_capacity) + 1) * 8) + 256;
+    return stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity)) + 256;
 }
 
 static bool force_general() {
@@ -471,15 +503,20 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
     sp += align256((size_t)(n_streams + 2) * 8);
     const int64_t max_tiles = tiles_for(out_capacity);
     P.tile_state = (unsigned long long*)sp;
-    P.ticket = (unsigned int*)(P.tile_state + max_tiles);
+    TileRec* rec = (TileRec*)(P.tile_state + max_tiles);
+    P.rec = rec;
+    P.ticket = (unsigned int*)(rec + max_tiles);
     P.max_tiles = max_tiles;
-    CUDA_TRY(cudaMemsetAsync(P.tile_state, 0, (size_t)(max_tiles + 1) * 8, stream));
+    CUDA_TRY(cudaMemsetAsync(P.tile_state, 0, tile_scratch_bytes(max_tiles), stream));
+    stream_tile_map_kernel<<<(unsigned)((n_streams + 255) / 256), 256, 0, stream>>>(chunk_off, n_chunks, stream_off, n_streams,
+                                                                                   rec, max_tiles);
+    LAUNCHED();
     static bool attr_set = false;
     if (!attr_set) {
         CUDA_TRY(cudaFuncSetAttribute(stream_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileShared)));
         attr_set = true;
     }
-    int64_t grid = 2 * (int64_t)sm_count();
+    int64_t grid = 4 * (int64_t)sm_count();
     if (grid > max_tiles) grid = max_tiles;
     stream_tile_kernel<<<(unsigned)grid, kTileThreads, sizeof(TileShared), stream>>>(P);
     LAUNCHED();

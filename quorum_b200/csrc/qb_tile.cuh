@@ -58,8 +58,15 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+__device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
     unsigned long long v;
     asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -113,12 +120,14 @@ struct Seg {
     uint16_t unit, final_;
 };
 // Written by the pre-pass: the units / bytes / items (chunks or requests) a tile owns.  u0p1 == 0: no unit starts here.
-struct TileRec {
+struct __align__(16) TileRec {
     int64_t u0p1, u1, b0, b1, c0, c1;
 };
 
 struct TileShared {
     uint64_t mbar;
+    uint64_t pad_;
+    TileRec next_rec;   // prefetched record of the CTA's next tile (cp.async)
     int64_t g0;         // absolute offset of the first staged byte (multiple of 32)
     int64_t u0, u1;     // unit range of this tile
     int64_t c0;         // (streams) absolute index of the tile's first chunk
@@ -285,14 +294,37 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
     if (tid == 0) mbar_init(&S.mbar, 1);
     __syncthreads();
 
+    // thread 0 keeps one ticket ahead: `cur` is this iteration's tile, `nxt` the next one, whose record is prefetched
+    int64_t cur = 0, nxt = 0;
+    bool have_rec = false;
+    if (tid == 0) cur = (int64_t)atomicAdd(P.ticket, 1u);
+#define QB_PREFETCH_REC()                                                     \
+    do {                                                                      \
+        have_rec = nxt < n_tiles;                                             \
+        if (have_rec) {                                                       \
+            const char* src_ = reinterpret_cast<const char*>(P.rec + nxt);    \
+            char* dst_ = reinterpret_cast<char*>(&S.next_rec);                \
+            cp_async16(dst_, src_);                                           \
+            cp_async16(dst_ + 16, src_ + 16);                                 \
+            cp_async16(dst_ + 32, src_ + 32);                                 \
+        }                                                                     \
+        cur = nxt;                                                            \
+    } while (0)
+
     for (;;) {
         // ---- take a tile ----
         __syncthreads();
         if (tid == 0) {
-            const int64_t tile = (int64_t)atomicAdd(P.ticket, 1u);
-            S.tile = (int32_t)tile;
+            const int64_t tile = cur;
+            S.tile = (int32_t)(tile < n_tiles ? tile : n_tiles);
             if (tile < n_tiles) {
-                const TileRec r = P.rec[tile];
+                TileRec r;
+                if (have_rec) {
+                    cp_async_wait_all();
+                    r = S.next_rec;
+                } else {
+                    r = P.rec[tile];
+                }
                 const int64_t nun = r.u0p1 ? r.u1 - (r.u0p1 - 1) : 0;
                 const int64_t g0 = r.b0 & ~(int64_t)31;
                 const bool fits = (r.b1 - g0) <= kStageCap;
@@ -318,6 +350,7 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
                     mbar_expect_tx(&S.mbar, bulk);
                     bulk_g2s(S.data, P.bytes + g0, bulk, &S.mbar);
                 }
+                nxt = (int64_t)atomicAdd(P.ticket, 1u);  // consumed later, by QB_PREFETCH_REC
             }
         }
         __syncthreads();
@@ -325,7 +358,10 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
         if (tile >= n_tiles) break;
         const int nunits = S.nunits;
         if (nunits == 0) {
-            if (tile == 0 && tid == 0) P.out_chunk_off[0] = 0;
+            if (tid == 0) {
+                if (tile == 0) P.out_chunk_off[0] = 0;
+                QB_PREFETCH_REC();
+            }
             if (wid == 0) lookback_exclusive(P.tile_state, tile, 0, lane);
             continue;
         }
@@ -358,6 +394,7 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
                 while (!mbar_try_wait(&S.mbar, parity)) {}
                 parity ^= 1;
             }
+            if (tid == 0) QB_PREFETCH_REC();  // the next ticket has long arrived: fetch that tile's record in the background
         }
         __syncthreads();
 
@@ -382,7 +419,7 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
                     const uint4* p = reinterpret_cast<const uint4*>(S.data + wb);
                     uint4 a = p[0], b = p[1];
                     lt = lt_mask16(a) | (lt_mask16(b) << 16);
-                    lt &= mask_ge(wb, lo_pos) & ~mask_ge(wb, hi_pos);
+                    if (wb < lo_pos || wb + 32 > hi_pos) lt &= mask_ge(wb, lo_pos) & ~mask_ge(wb, hi_pos);
                 }
                 S.ltbm[wi] = lt;
                 Tok r0{0, 0}, r1{0, 0};
@@ -431,9 +468,9 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
                 const int ub = S.u_beg[u], ue = S.u_end[u];
                 const int n = ue - ub;
                 const int64_t s = S.u0 + u;
-                const int64_t cfirst = P.stream_off[s];
-                const int64_t m = P.stream_off[s + 1] - cfirst;
-                const int64_t* co = P.chunk_off + cfirst;
+                const int cprev = u > 0 ? S.u_cend[u - 1] : 0;
+                const int64_t m = S.u_cend[u] - cprev;
+                const int64_t* co = P.chunk_off + (S.c0 + cprev);
                 const int64_t uabs = g0 + ub;
                 int32_t depth = 0;
                 int h = 0;
@@ -464,13 +501,7 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
                 };
                 auto emit = [&](int sa, int sb, int fin) {  // kept run [sa, sb) in unit coordinates
                     if (sb <= sa) return;
-                    const int a = ub + sa, b = ub + sb;
-                    const int w0 = a >> 5, w1 = (b - 1) >> 5;
-                    for (int w = w0 + lane; w <= w1; w += 32) {  // paint the kept bitmap
-                        uint32_t msk = mask_ge(w * 32, a) & ~mask_ge(w * 32, b);
-                        if (msk == 0xffffffffu) S.keptbm[w] = msk;
-                        else atomicOr(&S.keptbm[w], msk);
-                    }
+                    const int a = ub + sa;
                     const int len = sb - sa;
                     const int npieces = (len + kSegPiece - 1) / kSegPiece;
                     int slot = 0;
@@ -512,7 +543,15 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
                     cum = held_kept;
                     if (n > 0) {
                         const int st0 = ub >> 10, st1 = (ue - 1) >> 10;
-                        for (int st = st0; st <= st1; st++) {
+                        // steps of this unit that recorded tokens (lane j looks at steps st0+j and st0+32+j)
+                        const int ca = st0 + lane <= st1 ? S.step_tok[st0 + lane] : 0;
+                        const int cb = st0 + 32 + lane <= st1 ? S.step_tok[st0 + 32 + lane] : 0;
+                        unsigned long long live = (unsigned long long)__ballot_sync(kFull, ca > 0) |
+                                                  ((unsigned long long)__ballot_sync(kFull, cb > 0) << 32);
+                        while (live) {
+                            const int j = __ffsll((long long)live) - 1;
+                            live &= live - 1;
+                            const int st = st0 + j;
                             const int cnt = S.step_tok[st];
                             for (int k = 0; k < cnt; k++) {
                                 const Tok tk = S.tok[st * kSlots + k];
@@ -550,7 +589,21 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
 
         if (fastok2) {
             const int nsteps = S.nsteps;
-            // ---- C: kept bytes before every word (step_cum + wpre), then one thread per feed boundary ----
+            // ---- C: paint the kept bitmap from the segment pieces, kept bytes before every word (step_cum + wpre),
+            //         then one thread per feed boundary ----
+            {
+                const int nseg0 = S.nseg;
+                for (int i = wid; i < nseg0; i += kTileWarps) {
+                    const int a = (int)S.seg[i].src, b = a + (int)S.seg[i].len;
+                    const int w0 = a >> 5, w1 = (b - 1) >> 5;
+                    for (int w = w0 + lane; w <= w1; w += 32) {
+                        const uint32_t msk = mask_ge(w * 32, a) & ~mask_ge(w * 32, b);
+                        if (msk == 0xffffffffu) S.keptbm[w] = msk;
+                        else atomicOr(&S.keptbm[w], msk);
+                    }
+                }
+            }
+            __syncthreads();
             for (int st = wid; st < nsteps; st += kTileWarps) {
                 const int wi = st * 32 + lane;
                 const int pc = __popc(S.keptbm[wi]);
@@ -632,7 +685,8 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
                 }
             }
             __syncthreads();
-            // ---- D: unit output offsets inside the tile, tile aggregate, look-back ----
+            // ---- D: warp 0: unit output offsets inside the tile, tile aggregate, look-back;
+            //         meanwhile the other warps work out the carried state of every unit ----
             if (wid == 0) {
                 if (lane < nunits) S.u_out_rel[lane] = S.u_total[lane];
                 if (lane + 32 < nunits) S.u_out_rel[lane + 32] = S.u_total[lane + 32];
@@ -641,30 +695,14 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
                 const int64_t base = lookback_exclusive(P.tile_state, tile, tot, lane);
                 if (lane == 0) S.tile_base = base;
             }
-            __syncthreads();
-            // ---- E: offsets, state, bytes ----
-            const int64_t tbase = S.tile_base;
-            if (tile == 0 && tid == 0) P.out_chunk_off[0] = 0;
-            for (int i = tid; i < nb; i += kTileThreads) {
-                const int v = S.bnd[i];
-                P.out_chunk_off[S.c0 + 1 + i] = tbase + S.u_out_rel[v >> 24] + (v & 0xffffff);
-            }
-            const int nseg = S.nseg;
-            for (int i = wid; i < nseg; i += kTileWarps) {
-                const Seg sg = S.seg[i];
-                const int u = sg.unit;
-                int len = (int)sg.len;
-                if (sg.final_) {  // the unit's last kept run is clipped at the last release boundary
-                    const int lim = S.u_beg[u] + S.u_rlast[u] - (int)sg.src;
-                    if (lim < len) len = lim;
-                }
-                if (len > 0)
-                    warp_copy(P.out + tbase + S.u_out_rel[u] + sg.dst, S.data + sg.src, len, S.data + kStageCap + 64, lane);
-            }
-            for (int u = tid; u < nunits; u += kTileThreads) {
+            static_assert(kMaxUnits <= kTileThreads - 32, "one unit per thread of warps 1..");
+            StreamState so;
+            const int my_u = tid - 32;  // warps 1.. : one unit per thread
+            if (my_u >= 0 && my_u < nunits) {
+                const int u = my_u;
                 const int64_t s = S.u0 + u;
                 const int ub = S.u_beg[u], n = S.u_end[u] - ub;
-                const int64_t m = P.stream_off[s + 1] - P.stream_off[s];
+                const int m = S.u_cend[u] - (u > 0 ? S.u_cend[u - 1] : 0);
                 StreamState si;
                 if (P.st_in) {
                     si = P.st_in[s];
@@ -675,7 +713,6 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
                     for (int k = 0; k < kHeldMax; k++) si.held[k] = 0;
                 }
                 const int h = si.held_len;
-                StreamState so;
                 if (m == 0) {
                     so = si;
                     if (P.flags & 4u) so.held_len = 0;
@@ -684,10 +721,6 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
                 } else {
                     const HeldAcc A{S.data + ub, si.held, h};
                     const int depth = S.u_depth[u], lte = S.u_last_tok_end[u], rl = S.u_rlast[u];
-                    if (S.u_held_kept[u] && rl > -h) {  // carried literal bytes come first in the unit's output
-                        uint8_t* d = P.out + tbase + S.u_out_rel[u];
-                        for (int k = 0; k < h; k++) d[k] = si.held[k];
-                    }
                     int hp = INT32_MIN;
                     if (!(P.flags & 4u)) {
                         if (depth == 0) {
@@ -712,7 +745,37 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
                         for (int k = 0; k < so.held_len; k++) so.held[k] = A(hp + k);
                     }
                 }
-                if (P.st_out) P.st_out[s] = so;
+            }
+            __syncthreads();
+            // ---- E: per-chunk offsets, carried literal bytes, kept segments ----
+            const int64_t tbase = S.tile_base;
+            if (tile == 0 && tid == 0) P.out_chunk_off[0] = 0;
+            for (int i = tid; i < nb; i += kTileThreads) {
+                const int v = S.bnd[i];
+                P.out_chunk_off[S.c0 + 1 + i] = tbase + S.u_out_rel[v >> 24] + (v & 0xffffff);
+            }
+            const int nseg = S.nseg;
+            for (int i = wid; i < nseg; i += kTileWarps) {
+                const Seg sg = S.seg[i];
+                const int u = sg.unit;
+                int len = (int)sg.len;
+                if (sg.final_) {  // the unit's last kept run is clipped at the last release boundary
+                    const int lim = S.u_beg[u] + S.u_rlast[u] - (int)sg.src;
+                    if (lim < len) len = lim;
+                }
+                if (len > 0)
+                    warp_copy(P.out + tbase + S.u_out_rel[u] + sg.dst, S.data + sg.src, len, S.data + kStageCap + 64, lane);
+            }
+            if (my_u >= 0 && my_u < nunits) {
+                // carried bytes that turned out to be literal text come first in the unit's output; read them before the
+                // state is overwritten (state_out may alias state_in)
+                const int h = S.u_held_kept[my_u];
+                if (h && S.u_rlast[my_u] > -h) {
+                    const uint8_t* hb = P.st_in[S.u0 + my_u].held;
+                    uint8_t* d = P.out + tbase + S.u_out_rel[my_u];
+                    for (int k = 0; k < h; k++) d[k] = hb[k];
+                }
+                if (P.st_out) P.st_out[S.u0 + my_u] = so;
             }
         } else {
             stream_tile_general(P, S, tile, g0, staged, total);

@@ -402,7 +402,7 @@ static size_t stream_general_scratch_bytes(int64_t n_streams) {
 static int64_t tiles_for(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte_bound) / kWindow + 2; }
 
 // per tile: look-back state word + TileRec; plus the ticket
-static size_t tile_scratch_bytes(int64_t max_tiles) { return align256((size_t)max_tiles * (8 + sizeof(TileRec)) + 64); }
+static size_t tile_scratch_bytes(int64_t max_tiles) { return align256((size_t)(max_tiles + 1) * (8 + sizeof(TileRec)) + 64); }
 
 size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity) {
     (void)n_chunks;
@@ -503,7 +503,7 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
     sp += align256((size_t)(n_streams + 2) * 8);
     const int64_t max_tiles = tiles_for(out_capacity);
     P.tile_state = (unsigned long long*)sp;
-    TileRec* rec = (TileRec*)(P.tile_state + max_tiles);
+    TileRec* rec = (TileRec*)(P.tile_state + ((max_tiles + 1) & ~(int64_t)1));  // 16-byte aligned
     P.rec = rec;
     P.ticket = (unsigned int*)(rec + max_tiles);
     P.max_tiles = max_tiles;

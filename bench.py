@@ -340,7 +340,7 @@ def main():
         n_items = n_units
         out = torch.empty(total_in + len(sep_b) * n_units + 16, dtype=torch.uint8, device=dev)
         out_off = torch.empty(n_req + 1, dtype=torch.int64, device=dev)
-        scratch = torch.empty(qbatch.lib().qb200_strip_concat_scratch_bytes(n_units, n_req), dtype=torch.uint8, device=dev)
+        scratch = torch.empty(qbatch.lib().qb200_strip_concat_scratch_bytes(n_units, n_req, out.numel()), dtype=torch.uint8, device=dev)
 
         def step():
             qbatch.strip_concat_batch(table, data, in_off, req_off, sep, hide=True, streaming=False, out_bytes=out,

@@ -79,7 +79,7 @@ void qb200_tags_destroy(qb200_tags *tags);
  * Outputs: request q's text is out_bytes[out_off[q] .. out_off[q+1]) (out_off has n_req+1 entries, out_off[0]=0);
  * resp_out_len (optional, n_resp entries) receives each response's filtered length (0 for excluded ones).
  * out_capacity must be >= in_off[n_resp] + sep_len * n_resp.   in_bytes and out_bytes must be 16-byte aligned. */
-size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req);
+size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req, int64_t out_capacity);
 int qb200_strip_concat_batch(const qb200_tags *tags, const uint8_t *in_bytes, const int64_t *in_off, int64_t n_resp,
                              const int64_t *req_off, int64_t n_req, const uint8_t *sep, int32_t sep_len,
                              uint32_t flags, uint8_t *out_bytes, int64_t out_capacity, int64_t *out_off,

@@ -43,7 +43,7 @@ def lib() -> ctypes.CDLL:
     L.qb200_tags_destroy.restype = None
     L.qb200_tags_destroy.argtypes = [vp]
     L.qb200_strip_concat_scratch_bytes.restype = sz
-    L.qb200_strip_concat_scratch_bytes.argtypes = [i64, i64]
+    L.qb200_strip_concat_scratch_bytes.argtypes = [i64, i64, i64]
     L.qb200_strip_concat_batch.restype = ctypes.c_int
     L.qb200_strip_concat_batch.argtypes = [vp, vp, vp, i64, vp, i64, vp, i32, u32, vp, i64, vp, vp, vp, sz, vp]
     L.qb200_stream_feed_scratch_bytes.restype = sz

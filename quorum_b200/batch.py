@@ -111,7 +111,7 @@ def strip_concat_batch(tags: TagTable, in_bytes: torch.Tensor, in_off: torch.Ten
             out_off = torch.empty(n_req + 1, dtype=torch.int64, device=dev)
         if resp_out_len is None and want_resp_len:
             resp_out_len = torch.empty(max(n_resp, 1), dtype=torch.int64, device=dev)
-        need = lib().qb200_strip_concat_scratch_bytes(n_resp, n_req)
+        need = lib().qb200_strip_concat_scratch_bytes(n_resp, n_req, out_bytes.numel())
         if scratch is None or scratch.numel() < need:
             scratch = torch.empty(need, dtype=torch.uint8, device=dev)
         flags = (QB200_HIDE if hide else 0) | (QB200_STREAM_JOIN if streaming else 0)
@@ -272,7 +272,8 @@ class HostStripConcat:
         self.d_ro = torch.empty(max_req + 1, dtype=torch.int64, device=d)
         self.d_out = torch.empty(max_bytes + len(sep) * max_resp + 16, dtype=torch.uint8, device=d)
         self.d_oo = torch.empty(max_req + 1, dtype=torch.int64, device=d)
-        self.d_scratch = torch.empty(lib().qb200_strip_concat_scratch_bytes(max_resp, max_req), dtype=torch.uint8, device=d)
+        self.d_scratch = torch.empty(lib().qb200_strip_concat_scratch_bytes(max_resp, max_req, self.d_out.numel()),
+                                     dtype=torch.uint8, device=d)
         self.h_out = torch.empty(self.d_out.numel(), dtype=torch.uint8).pin_memory()
         self.h_oo = torch.empty(max_req + 1, dtype=torch.int64).pin_memory()
 

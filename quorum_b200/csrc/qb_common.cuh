@@ -273,8 +273,10 @@ __device__ __forceinline__ uint32_t mask_ge(int64_t wb, int64_t p) {
     return d <= 0 ? 0xffffffffu : (d >= 32 ? 0u : (0xffffffffu << (int)d));
 }
 
-// Warp-cooperative byte copy dst[0..n) = src[0..n).  16-byte stores on the aligned middle of dst; the source is read
-// as aligned 32-bit words and realigned with a funnel shift.  src_lo/src_hi bound what may be read.
+// Warp-cooperative byte copy dst[0..n) = src[0..n) (src and dst uniform across the warp).  16-byte stores on the aligned
+// middle of dst; the source is read as aligned 16-byte vectors and realigned with a word select + funnel shift.
+// [.., src_hi) bounds what may be read.
+template <bool PREFETCH = false>
 __device__ inline void warp_copy(uint8_t* dst, const uint8_t* src, int64_t n, const uint8_t* src_hi, int lane) {
     if (n <= 0) return;
     int64_t head = (16 - (reinterpret_cast<uintptr_t>(dst) & 15)) & 15;
@@ -283,25 +285,38 @@ __device__ inline void warp_copy(uint8_t* dst, const uint8_t* src, int64_t n, co
     dst += head;
     src += head;
     n -= head;
-    int shift = (int)(reinterpret_cast<uintptr_t>(src) & 3);
-    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src - shift);
+    const int shift = (int)(reinterpret_cast<uintptr_t>(src) & 15);
+    const uint4* s128 = reinterpret_cast<const uint4*>(src - shift);
     int64_t nvec = n >> 4;
-    // the realigning read touches 4 bytes past the vector when shift != 0: keep that inside [.., src_hi)
-    while (nvec > 0 && shift != 0 && reinterpret_cast<const uint8_t*>(s32 + 4 * nvec + 1) > src_hi) nvec--;
+    // the realigning read touches the next 16-byte vector when shift != 0: keep that inside [.., src_hi)
+    if (shift != 0) {
+        const int64_t room = (src_hi - reinterpret_cast<const uint8_t*>(s128)) >> 4;  // whole vectors readable
+        if (nvec + 1 > room) nvec = room > 0 ? room - 1 : 0;
+    }
     uint4* d4 = reinterpret_cast<uint4*>(dst);
+    const int wsel = shift >> 2, sh = (shift & 3) * 8;
+    if (PREFETCH && nvec > 32) {  // more than one round of loads: get every line moving before the first store waits
+        const uint8_t* base = reinterpret_cast<const uint8_t*>(s128);
+        const int64_t bytes = (nvec + 1) << 4;
+        for (int64_t o = (int64_t)lane * 128; o < bytes; o += 32 * 128)
+            asm volatile("prefetch.L1 [%0];" ::"l"(base + o));  // generic address: a no-op for shared memory
+    }
     for (int64_t v = lane; v < nvec; v += 32) {
-        const uint32_t* p = s32 + 4 * v;
-        uint32_t a0 = p[0], a1 = p[1], a2 = p[2], a3 = p[3];
-        uint4 o;
+        const uint4 A = s128[v];
+        uint4 o = A;
         if (shift) {
-            uint32_t a4 = p[4];
-            int sh = shift * 8;
-            o.x = __funnelshift_r(a0, a1, sh);
-            o.y = __funnelshift_r(a1, a2, sh);
-            o.z = __funnelshift_r(a2, a3, sh);
-            o.w = __funnelshift_r(a3, a4, sh);
-        } else {
-            o = make_uint4(a0, a1, a2, a3);
+            const uint4 B = s128[v + 1];
+            uint32_t w0, w1, w2, w3, w4;
+            switch (wsel) {
+                case 0: w0 = A.x; w1 = A.y; w2 = A.z; w3 = A.w; w4 = B.x; break;
+                case 1: w0 = A.y; w1 = A.z; w2 = A.w; w3 = B.x; w4 = B.y; break;
+                case 2: w0 = A.z; w1 = A.w; w2 = B.x; w3 = B.y; w4 = B.z; break;
+                default: w0 = A.w; w1 = B.x; w2 = B.y; w3 = B.z; w4 = B.w; break;
+            }
+            o.x = __funnelshift_r(w0, w1, sh);
+            o.y = __funnelshift_r(w1, w2, sh);
+            o.z = __funnelshift_r(w2, w3, sh);
+            o.w = __funnelshift_r(w3, w4, sh);
         }
         d4[v] = o;
     }

@@ -9,6 +9,40 @@
 
 namespace qb {
 
+// Token records written by the tokenizer pass (qb_tok.cuh), one group per absolute 1 KiB step of the flat buffer:
+//   cnt[step]  number of records (0..kRecPerStep), kRecOverflow when the step had more '<' than fit
+//   rec[step * kRecPerStep + k], in position order:
+//     bits 0-9 position inside the step | 10-16 tag length in bytes (0 for a literal '<') | 17-18 kind
+//     (0 open tag, 1 close tag, 2 '<' that starts no complete tag) | 19-25 backreference class | 26 the tag uses a
+//     U+0130/U+0131/U+017F spelling (the walker re-reads the bytes when that matters)
+constexpr int kRecPerStep = 8;
+constexpr int kRecOverflow = 255;
+struct TokSrc {
+    const uint8_t* cnt = nullptr;
+    const uint32_t* rec = nullptr;
+};
+__device__ __forceinline__ uint32_t rec_select(const uint4& a, const uint4& b, int k) {
+    switch (k) {
+        case 0: return a.x;
+        case 1: return a.y;
+        case 2: return a.z;
+        case 3: return a.w;
+        case 4: return b.x;
+        case 5: return b.y;
+        case 6: return b.z;
+        default: return b.w;
+    }
+}
+// true when any step touched by the unit [ustart, ustart+n) overflowed its record slots (then the unit is walked
+// the slow way, straight from its bytes)
+__device__ inline bool unit_has_overflow(const TokSrc& ts, int64_t ustart, int64_t n, int lane) {
+    if (!ts.cnt || n <= 0) return false;
+    const int64_t s0 = ustart >> 10, s1 = (ustart + n - 1) >> 10;
+    bool bad = false;
+    for (int64_t s = s0 + lane; s <= s1; s += 32) bad |= ts.cnt[s] == kRecOverflow;
+    return __any_sync(kFull, bad);
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // strip_thinking_tags  (oai_proxy.py:120-139), SURVEY.md Appendix A.1
 //
@@ -22,7 +56,7 @@ struct StripResult {
     int64_t kept_len;   // output length after filter + strip
 };
 
-template <bool COPY>
+template <bool COPY, bool TOK = false>
 struct StripWalker {
     const DevTags& tg;
     const uint8_t* buf;   // flat buffer base (16-byte aligned)
@@ -37,6 +71,7 @@ struct StripWalker {
     StripResult res{0, 0};
     // copy pass
     uint8_t* dst = nullptr;
+    TokSrc ts;  // when set: tags come from the tokenizer's records instead of rescanning the bytes
 
     __device__ StripWalker(const DevTags& tg_, const uint8_t* buf_, int64_t total_, int64_t ustart_, int64_t n_,
                            unsigned long long* lc, int lane_)
@@ -80,7 +115,7 @@ struct StripWalker {
             if (s < res.first_pos) s = res.first_pos;
             int64_t take = e - s;
             if (take > res.kept_len - cum) take = res.kept_len - cum;
-            if (take > 0) warp_copy(dst + cum, T.p + s, take, buf + total, lane);
+            if (take > 0) warp_copy<true>(dst + cum, T.p + s, take, buf + total, lane);
             cum += e - s;
         } else {
             if (!lead_done) {
@@ -96,8 +131,78 @@ struct StripWalker {
         }
     }
 
+    // walker state of pass B
+    int state = -1;
+    int64_t seg_start = 0;
+    __device__ __forceinline__ void event(int64_t x, int64_t tend, int cls, bool is_close) {
+        if (state < 0) {
+            if (!is_close && lastclose[cls] > (unsigned long long)x) {
+                emit(seg_start, x);
+                state = cls;
+            }
+        } else if (is_close && cls == state) {
+            seg_start = tend;
+            state = -1;
+        }
+    }
+
+    // Token mode: lane j holds the records of step S0 + j of the current group of 32 steps.
+    __device__ void run_tokens() {
+        const int64_t s_first = ustart >> 10, s_last = (ustart + n - 1) >> 10;
+        for (int c = lane; c < tg.ncls; c += 32) lastclose[c] = 0;
+        __syncwarp();
+        for (int pass = 0; pass < 2; pass++) {
+            for (int64_t S0 = s_first; S0 <= s_last; S0 += 32) {
+                const int64_t sj = S0 + lane;
+                int cnt = 0;
+                uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
+                if (sj <= s_last) {
+                    cnt = ts.cnt[sj];
+                    if (cnt > 0) {
+                        const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);
+                        ra = rp[0];
+                        if (cnt > 4) rb = rp[1];
+                    }
+                }
+                if (pass == 0) {  // pass A: last closer per class, every lane over its own step
+                    for (int k = 0; k < cnt; k++) {
+                        const uint32_t r = rec_select(ra, rb, k);
+                        if (((r >> 17) & 3) != 1) continue;
+                        const int64_t x = (sj << 10) + (r & 1023) - ustart;
+                        const int64_t tend = x + ((r >> 10) & 127);
+                        if (x >= 0 && tend <= n) atomicMax(&lastclose[(r >> 19) & 127], (unsigned long long)(x + 1));
+                    }
+                } else {  // pass B: tokens in position order
+                    unsigned live = __ballot_sync(kFull, cnt > 0);
+                    while (live) {
+                        const int j = __ffs(live) - 1;
+                        live &= live - 1;
+                        const int c = __shfl_sync(kFull, cnt, j);
+#pragma unroll
+                        for (int k = 0; k < kRecPerStep; k++) {
+                            if (k >= c) break;
+                            const uint32_t r = __shfl_sync(kFull, rec_select(ra, rb, k), j);
+                            const int kind = (r >> 17) & 3;
+                            if (kind == 2) continue;
+                            const int64_t x = ((S0 + j) << 10) + (r & 1023) - ustart;
+                            const int64_t tend = x + ((r >> 10) & 127);
+                            if (x < 0 || tend > n) continue;
+                            event(x, tend, (r >> 19) & 127, kind == 1);
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        emit(seg_start, n);
+    }
+
     __device__ void run() {
         if (n <= 0) return;
+        if (TOK) {
+            run_tokens();
+            return;
+        }
         const int64_t w_first = ustart >> 5, w_last = (ustart + n - 1) >> 5;
         const int64_t nsteps = (w_last - w_first + 32) >> 5;
         for (int c = lane; c < tg.ncls; c += 32) lastclose[c] = 0;
@@ -117,8 +222,6 @@ struct StripWalker {
         }
         __syncwarp();
         // pass B: walk tokens in order
-        int state = -1;
-        int64_t seg_start = 0;
         for (int64_t s = 0; s < nsteps; s++) {
             int64_t wb;
             uint32_t m = step_mask(w_first, w_last, s, wb);
@@ -152,17 +255,7 @@ struct StripWalker {
                 x = __shfl_sync(kFull, x, src);
                 tend = __shfl_sync(kFull, tend, src);
                 kc = __shfl_sync(kFull, kc, src);
-                const int cls = kc & 0xff;
-                const bool is_close = (kc & 0x100) != 0;
-                if (state < 0) {
-                    if (!is_close && lastclose[cls] > (unsigned long long)x) {
-                        emit(seg_start, x);
-                        state = cls;
-                    }
-                } else if (is_close && cls == state) {
-                    seg_start = tend;
-                    state = -1;
-                }
+                event(x, tend, kc & 0xff, (kc & 0x100) != 0);
                 act = __ballot_sync(kFull, tok != 0);
             }
         }
@@ -185,7 +278,7 @@ struct StreamResult {
     int64_t total_out;  // kept bytes released by this call
 };
 
-template <bool COPY>
+template <bool COPY, bool TOK = false>
 struct StreamWalker {
     const DevTags& tg;
     const uint8_t* buf;
@@ -199,6 +292,8 @@ struct StreamWalker {
     int64_t out_base = 0;            // absolute output offset of this stream
     int64_t* out_chunk_off = nullptr;  // global array, indexed by absolute chunk index
     int64_t chunk0 = 0;              // absolute index of this stream's first chunk
+    TokSrc ts;                       // when set: tags come from the tokenizer's records instead of rescanning the bytes
+    bool overflow = false;           // token mode: a step of this unit had more '<' than record slots (result invalid)
 
     __device__ StreamWalker(const DevTags& tg_, const uint8_t* buf_, int64_t total_, const int64_t* co_, int64_t m_,
                             int lane_, uint32_t flags_)
@@ -281,91 +376,150 @@ struct StreamWalker {
 
         int64_t cum = held_kept;   // kept bytes before the current step (carried literal included)
         int64_t out_pos = held_kept;  // copy pass: next output byte (carried literal bytes come first)
-        int64_t kb = 1;            // next feed boundary to account (co[kb] is the end of chunk kb-1)
+        int64_t kb = COPY ? 1 : m;  // next feed boundary to account (co[kb] is the end of chunk kb-1)
         int64_t R_last = 0;        // release boundary of the last feed
         int64_t P_last = 0;        // kept bytes before R_last
         bool have_last = false;    // this lane accounted the last boundary
         uint32_t prev_lt31 = 0, prev_kept31 = 0;
         if (COPY && lane == 0) out_chunk_off[chunk0] = out_base;
 
-        const int64_t w_first = ustart >> 5;
+        const int64_t w_first = (ustart >> 10) << 5;  // steps sit on the absolute 1 KiB grid (the tokenizer's grid)
         const int64_t w_last = n > 0 ? ((ustart + n - 1) >> 5) : (w_first - 1);
         const int64_t nsteps = n > 0 ? ((w_last - w_first + 32) >> 5) : 1;  // one (empty) step accounts empty chunks
+        constexpr bool tokmode = TOK;
+        // feed boundaries are fetched one step ahead: cpre = co[pre_base + lane]
+        int64_t pre_base = kb;
+        int64_t cpre = (kb + lane <= m) ? co[kb + lane] - ustart : INT64_MAX;
+        int g_cnt = 0;  // token mode: this lane's records of step (group start + lane)
+        uint4 g_ra = make_uint4(0, 0, 0, 0), g_rb = g_ra;
         for (int64_t s = 0; s < nsteps; s++) {
             const int64_t w = w_first + s * 32 + lane;
             const int64_t wb = (w << 5) - ustart;
             const uint32_t range = (w <= w_last) ? (mask_ge(wb, 0) & ~mask_ge(wb, n)) : 0u;
-            const uint32_t lt = (w <= w_last) ? (load_lt_word(buf, total, w) & range) : 0u;
-            uint32_t tok = 0;
-            {
-                uint32_t mm = lt & mask_ge(wb, skip_until);
-                while (mm) {
-                    int b = __ffs(mm) - 1;
-                    mm &= mm - 1;
-                    int cls;
-                    int64_t ex;
-                    if (match_tag(tg, T, wb + b, n, false, cls, ex) >= 0 || match_tag(tg, T, wb + b, n, true, cls, ex) >= 0)
-                        tok |= 1u << b;
-                }
-            }
+            uint32_t lt = 0;
             uint32_t kept = depth == 0 ? mask_ge(wb, skip_until) : 0u;
-            unsigned act = __ballot_sync(kFull, tok != 0);
-            while (act) {
-                int src = __ffs(act) - 1;
-                int64_t x = 0, tend = 0, ex = -1;
-                int is_close = 0;
-                if (lane == src) {
-                    int b = __ffs(tok) - 1;
-                    tok &= tok - 1;
-                    x = wb + b;
-                    int cls;
-                    tend = match_tag(tg, T, x, n, false, cls, ex);
-                    if (tend < 0) {
-                        tend = match_tag(tg, T, x, n, true, cls, ex);
-                        is_close = 1;
+            // one recognised-or-not tag at unit position x
+            auto on_tag = [&](int64_t x, int64_t tend, bool is_close, int64_t ex) {
+                if (!recognised(is_close, x, tend, ex)) return;
+                if (depth == 0) {  // open tag at depth 0: the kept run ends at x
+                    kept &= ~mask_ge(wb, x);
+                    if (COPY) {
+                        int64_t len = x - seg_start;
+                        if (len > 0) warp_copy<true>(dst + out_pos, T.p + seg_start, len, buf + total, lane);
+                        out_pos += len > 0 ? len : 0;
+                    }
+                    depth = 1;
+                } else {
+                    depth += is_close ? -1 : 1;
+                    if (depth == 0) {
+                        kept |= mask_ge(wb, tend);
+                        seg_start = tend;
                     }
                 }
-                x = __shfl_sync(kFull, x, src);
-                tend = __shfl_sync(kFull, tend, src);
-                ex = __shfl_sync(kFull, ex, src);
-                is_close = __shfl_sync(kFull, is_close, src);
-                if (recognised(is_close != 0, x, tend, ex)) {
-                    if (depth == 0) {  // open tag at depth 0: the kept run ends at x
-                        kept &= ~mask_ge(wb, x);
-                        if (COPY) {
-                            int64_t len = x - seg_start;
-                            if (len > 0) warp_copy(dst + out_pos, T.p + seg_start, len, buf + total, lane);
-                            out_pos += len > 0 ? len : 0;
-                        }
-                        depth = 1;
-                    } else {
-                        depth += is_close ? -1 : 1;
-                        if (depth == 0) {
-                            kept |= mask_ge(wb, tend);
-                            seg_start = tend;
+                last_tok_end = skip_until = tend;
+            };
+            if (tokmode) {
+                if ((s & 31) == 0) {  // fetch the records of the next 32 steps, one step per lane
+                    const int64_t sj = (w_first >> 5) + s + lane;
+                    g_cnt = 0;
+                    if (n > 0 && sj <= ((ustart + n - 1) >> 10)) {
+                        g_cnt = ts.cnt[sj];
+                        if (g_cnt == kRecOverflow) g_cnt = -1;
+                        if (g_cnt > 0) {
+                            const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);
+                            g_ra = rp[0];
+                            if (g_cnt > 4) g_rb = rp[1];
                         }
                     }
-                    last_tok_end = skip_until = tend;
+                    if (__any_sync(kFull, g_cnt < 0)) {  // stop before anything derived from missing records is written
+                        overflow = true;
+                        return res;
+                    }
                 }
-                act = __ballot_sync(kFull, tok != 0);
+                const int j = (int)(s & 31);
+                const int c = __shfl_sync(kFull, g_cnt, j);
+#pragma unroll
+                for (int k = 0; k < kRecPerStep; k++) {
+                    if (k >= c) break;
+                    const uint32_t r = __shfl_sync(kFull, rec_select(g_ra, g_rb, k), j);
+                    const int pos = (int)(r & 1023);
+                    const int64_t x = ((w_first + s * 32) << 5) + pos - ustart;
+                    if (x < 0 || x >= n) continue;
+                    if (lane == (pos >> 5)) lt |= 1u << (pos & 31);
+                    const int kind = (r >> 17) & 3;
+                    const int64_t tend = x + ((r >> 10) & 127);
+                    if (kind == 2 || tend > n || x < skip_until) continue;  // literal '<', or a tag cut by the unit end
+                    int64_t ex = -1;
+                    if (((r >> 26) & 1) && depth == 0 && kind == 0) {  // rare: which letter uses a non-ASCII form?
+                        int cls;
+                        match_tag(tg, T, x, n, false, cls, ex);
+                    }
+                    on_tag(x, tend, kind == 1, ex);
+                }
+            } else {
+                lt = (w <= w_last) ? (load_lt_word(buf, total, w) & range) : 0u;
+                uint32_t tok = 0;
+                {
+                    uint32_t mm = lt & mask_ge(wb, skip_until);
+                    while (mm) {
+                        int b = __ffs(mm) - 1;
+                        mm &= mm - 1;
+                        int cls;
+                        int64_t ex;
+                        if (match_tag(tg, T, wb + b, n, false, cls, ex) >= 0 || match_tag(tg, T, wb + b, n, true, cls, ex) >= 0)
+                            tok |= 1u << b;
+                    }
+                }
+                unsigned act = __ballot_sync(kFull, tok != 0);
+                while (act) {
+                    int src = __ffs(act) - 1;
+                    int64_t x = 0, tend = 0, ex = -1;
+                    int is_close = 0;
+                    if (lane == src) {
+                        int b = __ffs(tok) - 1;
+                        tok &= tok - 1;
+                        x = wb + b;
+                        int cls;
+                        tend = match_tag(tg, T, x, n, false, cls, ex);
+                        if (tend < 0) {
+                            tend = match_tag(tg, T, x, n, true, cls, ex);
+                            is_close = 1;
+                        }
+                    }
+                    x = __shfl_sync(kFull, x, src);
+                    tend = __shfl_sync(kFull, tend, src);
+                    ex = __shfl_sync(kFull, ex, src);
+                    is_close = __shfl_sync(kFull, is_close, src);
+                    on_tag(x, tend, is_close != 0, ex);
+                    act = __ballot_sync(kFull, tok != 0);
+                }
             }
             kept &= range;
-            // exclusive prefix of kept counts over the words of this step
-            int pc = __popc(kept), incl = pc;
+            // exclusive prefix of kept counts over the words of this step (the count pass only needs it where the
+            // unit's last feed boundary lies: the released total depends on nothing else)
+            const int pc = __popc(kept);
+            int incl = pc, excl = 0, step_total;
+            const bool need_scan = COPY || s == nsteps - 1;
+            if (need_scan) {
 #pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                int v = __shfl_up_sync(kFull, incl, d);
-                if (lane >= d) incl += v;
+                for (int d = 1; d < 32; d <<= 1) {
+                    int v = __shfl_up_sync(kFull, incl, d);
+                    if (lane >= d) incl += v;
+                }
+                excl = incl - pc;
+                step_total = __shfl_sync(kFull, incl, 31);
+            } else {
+                step_total = (int)__reduce_add_sync(kFull, (unsigned)pc);
             }
-            const int excl = incl - pc;
-            const int step_total = __shfl_sync(kFull, incl, 31);
             const int64_t step_end = wb - (int64_t)lane * 32 + 1024 < n ? wb - (int64_t)lane * 32 + 1024 : n;
             const int64_t step_wb0 = wb - (int64_t)lane * 32;
 
             // ---- feed boundaries whose last byte lies in this step (c == 0: before any byte) ----
-            for (;;) {
+            for (; need_scan;) {
                 const int64_t k = kb + lane;
-                const int64_t c = k <= m ? co[k] - ustart : INT64_MAX;
+                int64_t c;
+                if (kb == pre_base) c = cpre;
+                else c = k <= m ? co[k] - ustart : INT64_MAX;
                 const bool in = k <= m && c <= step_end;
                 // word (lane index inside this step) that holds byte c-1
                 int lw = (in && c > 0) ? (int)((c - 1 - step_wb0) >> 5) : 0;
@@ -416,6 +570,10 @@ struct StreamWalker {
                 kb += __popc(inb);
                 if (inb != kFull) break;
             }
+            if (need_scan && kb != pre_base) {  // issue the next step's boundary loads now, use them a step later
+                pre_base = kb;
+                cpre = (kb + lane <= m) ? co[kb + lane] - ustart : INT64_MAX;
+            }
             cum += step_total;
             prev_lt31 = __shfl_sync(kFull, lt, 31);
             prev_kept31 = __shfl_sync(kFull, kept, 31);
@@ -436,7 +594,7 @@ struct StreamWalker {
             if (depth == 0) {
                 int64_t e = R_last < n ? R_last : n;
                 int64_t len = e - seg_start;
-                if (len > 0) warp_copy(dst + out_pos, T.p + seg_start, len, buf + total, lane);
+                if (len > 0) warp_copy<true>(dst + out_pos, T.p + seg_start, len, buf + total, lane);
             }
             if (st_out) {
                 // what stays carried
@@ -470,6 +628,310 @@ struct StreamWalker {
                     }
                     *st_out = so;
                 }
+            }
+        }
+        return res;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------------------------
+// Record-driven stream walker ("run list"): the fast path of ThinkingTagFilter.feed.
+//
+// Same semantics as StreamWalker, different shape of work: nothing here loops over the text.
+//   1  the warp walks the unit's token records (only steps that have any) and collects the kept runs of the unit,
+//      one run per lane (more than 32 runs, or a step whose records overflowed: `overflow`, the caller falls back to
+//      StreamWalker); the source lines of the runs are prefetched right away;
+//   2  the feed boundaries are handled 32 at a time, one per lane: released bytes before c = carried literal bytes +
+//      overlap of [0, c) with the runs; the hold-back test looks up the last '<' before c in the step's records;
+//   3  the runs are copied to their final place with 16-byte stores; carried state is written.
+// The count pass is phase 1 plus the last boundary.  Positions are unit-relative int32 (units of 2 GiB and more take
+// the fallback).
+// ------------------------------------------------------------------------------------------------------------------
+template <bool COPY>
+struct StreamRunWalker {
+    const DevTags& tg;
+    const uint8_t* buf;
+    int64_t total;
+    const int64_t* co;
+    int64_t m;
+    int lane;
+    uint32_t flags;
+    TokSrc ts;
+    bool overflow = false;
+    uint8_t* dst = nullptr;
+    int64_t out_base = 0;
+    int64_t* out_chunk_off = nullptr;
+    int64_t chunk0 = 0;
+
+    __device__ StreamRunWalker(const DevTags& tg_, const uint8_t* buf_, int64_t total_, const int64_t* co_, int64_t m_, int lane_,
+                               uint32_t flags_, TokSrc ts_)
+        : tg(tg_), buf(buf_), total(total_), co(co_), m(m_), lane(lane_), flags(flags_), ts(ts_) {}
+
+    __device__ StreamResult run(const StreamState* st_in, StreamState* st_out) {
+        StreamState si;
+        if (st_in) {
+            si = *st_in;
+        } else {
+            si.depth = 0;
+            si.tail_len = -1;
+            si.held_len = 0;
+            for (int i = 0; i < kHeldMax; i++) si.held[i] = 0;
+        }
+        StreamResult res{0};
+        if (m <= 0) {  // nothing fed: state passes through
+            if (COPY && st_out && lane == 0) {
+                if (flags & 4u) si.held_len = 0;
+                for (int i = si.held_len; i < kHeldMax; i++) si.held[i] = 0;
+                si.tail_len = -1;
+                *st_out = si;
+            }
+            return res;
+        }
+        const int64_t ustart = co[0];
+        const int64_t n64 = co[m] - ustart;
+        if (n64 >= (int64_t)1 << 31) {
+            overflow = true;
+            return res;
+        }
+        const int n = (int)n64;
+        const int h = si.held_len;
+        const uint8_t* heldp = st_in ? st_in->held : buf;
+        const HeldAcc A{buf + ustart, heldp, h};
+        const PtrAcc T{buf + ustart};
+
+        int depth = si.depth;
+        int last_tok_end = -1, seg_start = 0, held_kept = 0;
+        bool held_unconsumed = false;
+        // runs: lane i keeps run i = [run_s, run_e) and run_cum = released-candidate bytes before it
+        int run_s = 0, run_e = 0, run_cum = 0, nruns = 0, cum = 0;
+
+        auto first_boundary_after = [&](int64_t pos) -> int64_t {
+            int64_t lo = 1, hi = m + 1;
+            while (lo < hi) {
+                int64_t mid = (lo + hi) >> 1;
+                if (co[mid] - ustart > pos) hi = mid;
+                else lo = mid + 1;
+            }
+            return lo;
+        };
+        auto recognised = [&](bool is_close, int x, int tend, int ex) -> bool {
+            if (is_close) return depth > 0;
+            if (depth > 0) return true;
+            if (tg.hold_enabled && ex < 0) return true;
+            const int64_t lo = tg.hold_enabled ? ex : x;
+            int64_t k = first_boundary_after(lo);
+            return !(k <= m && co[k] - ustart < tend);
+        };
+        auto close_run = [&](int e) {
+            if (e > seg_start) {
+                if (lane == nruns) {
+                    run_s = seg_start;
+                    run_e = e;
+                    run_cum = cum;
+                }
+                if (COPY) {  // get the run's source lines moving; they are copied after the boundary work
+                    const uint8_t* a = T.p + seg_start;
+                    const uint8_t* base = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(a) & ~(uintptr_t)127);
+                    const int64_t bytes = (a - base) + (e - seg_start);
+                    for (int64_t o = (int64_t)lane * 128; o < bytes; o += 32 * 128) asm volatile("prefetch.L2 [%0];" ::"l"(base + o));
+                }
+                nruns++;
+                cum += e - seg_start;
+            }
+        };
+        auto on_tag = [&](int x, int tend, bool is_close, int ex) {
+            if (!recognised(is_close, x, tend, ex)) return;
+            if (depth == 0) {
+                close_run(x);
+                depth = 1;
+            } else {
+                depth += is_close ? -1 : 1;
+                if (depth == 0) seg_start = tend;
+            }
+            last_tok_end = tend;
+        };
+
+        // ---- the carried partial tag (positions -h .. -1) ----
+        if (h > 0) {
+            int cls;
+            int64_t ex;
+            int64_t tend = match_tag(tg, A, -h, n, false, cls, ex);
+            bool is_close = false;
+            if (tend < 0 && depth > 0) {
+                tend = match_tag(tg, A, -h, n, true, cls, ex);
+                is_close = true;
+            }
+            if (tend >= 0 && recognised(is_close, -h, (int)tend, (int)ex)) {
+                depth += is_close ? -1 : 1;
+                last_tok_end = seg_start = (int)tend;
+            } else {
+                held_unconsumed = true;
+                if (depth == 0) held_kept = h;
+            }
+        }
+        cum = held_kept;
+
+        // ---- 1: token records of the unit, steps with records only ----
+        if (n > 0) {
+            const int64_t s_first = ustart >> 10, s_last = (ustart + n - 1) >> 10;
+            for (int64_t S0 = s_first; S0 <= s_last; S0 += 32) {
+                const int64_t sj = S0 + lane;
+                int cnt = 0;
+                uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
+                if (sj <= s_last) {
+                    cnt = ts.cnt[sj];
+                    if (cnt == kRecOverflow) cnt = -1;
+                    if (cnt > 0) {
+                        const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);
+                        ra = rp[0];
+                        if (cnt > 4) rb = rp[1];
+                    }
+                }
+                if (__any_sync(kFull, cnt < 0)) {
+                    overflow = true;
+                    return res;
+                }
+                unsigned live = __ballot_sync(kFull, cnt > 0);
+                while (live) {
+                    const int j = __ffs(live) - 1;
+                    live &= live - 1;
+                    const int c = __shfl_sync(kFull, cnt, j);
+                    const int sb = (int)(((S0 + j) << 10) - ustart);  // unit position of the step's first byte
+#pragma unroll
+                    for (int k = 0; k < kRecPerStep; k++) {
+                        if (k >= c) break;
+                        const uint32_t r = __shfl_sync(kFull, rec_select(ra, rb, k), j);
+                        const int kind = (r >> 17) & 3;
+                        const int x = sb + (int)(r & 1023);
+                        const int tend = x + (int)((r >> 10) & 127);
+                        if (kind == 2 || x < 0 || tend > n || x < last_tok_end) continue;  // literal '<' / cut by the unit
+                        int ex = -1;
+                        if (((r >> 26) & 1) && depth == 0 && kind == 0) {  // rare: which letter uses a non-ASCII form?
+                            int cls;
+                            int64_t e64;
+                            match_tag(tg, T, x, n, false, cls, e64);
+                            ex = (int)e64;
+                        }
+                        on_tag(x, tend, kind == 1, ex);
+                    }
+                }
+            }
+        }
+        const int nclosed = nruns;       // runs ended by an open tag
+        if (depth == 0) close_run(n);    // the final run, clipped later at the last release boundary
+        const bool has_final = nruns > nclosed;
+        if (nruns > 32) {
+            overflow = true;
+            return res;
+        }
+
+        // ---- 2: feed boundaries, one per lane ----
+        int R_last = 0, P_last = 0;
+        bool have_last = false;
+        if (COPY && lane == 0) out_chunk_off[chunk0] = out_base;
+        for (int64_t kb = COPY ? 1 : m; kb <= m; kb += 32) {
+            const int64_t k = kb + lane;
+            const bool in = k <= m;
+            const int c = in ? (int)(co[k] - ustart) : 0;
+            // last '<' in [c - kHeldMax, c): look through the records of the step that holds byte c-1 and, when the
+            // window reaches back into it, of the step before (per lane, no warp-wide operation in here)
+            int p = -1;
+            if (in && c > 0) {
+                const int64_t sj = (ustart + c - 1) >> 10;
+#pragma unroll
+                for (int back = 0; back < 2; back++) {
+                    const int64_t sx = sj - back;
+                    if (back == 1 && (p >= 0 || sx < (ustart >> 10) || ((sj << 10) - ustart) <= c - kHeldMax)) break;
+                    const int cnt = ts.cnt[sx];
+                    if (cnt == 0) continue;
+                    const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sx * kRecPerStep);
+                    const uint4 qa = rp[0];
+                    uint4 qb = make_uint4(0, 0, 0, 0);
+                    if (cnt > 4) qb = rp[1];
+                    const int sb = (int)((sx << 10) - ustart);
+                    for (int q = 0; q < cnt; q++) {
+                        const int x = sb + (int)(rec_select(qa, qb, q) & 1023);
+                        if (x >= 0 && x < c && x > p) p = x;
+                    }
+                }
+            }
+            // released-candidate bytes before c: carried literal bytes + overlap of [0, c) with the runs; and is the
+            // '<' at p kept text (inside a run)?  One uniform loop over the runs for both.
+            int P = held_kept;
+            bool p_kept = false;
+            for (int i = 0; i < nruns; i++) {
+                const int rs = __shfl_sync(kFull, run_s, i), re = __shfl_sync(kFull, run_e, i);
+                const int hi = c < re ? c : re;
+                if (hi > rs) P += hi - rs;
+                p_kept |= (p >= rs && p < re);
+            }
+            int R = c;
+            const bool found_lt = p >= 0;
+            if (found_lt && p_kept && c - p <= kHeldMax && tg.hold_enabled && is_tag_prefix(tg, T, p, c, true, false)) {
+                R = p;
+                P -= (c - p);
+            }
+            if (in && !found_lt && held_kept && tg.hold_enabled && c + h <= kHeldMax && is_tag_prefix(tg, A, -h, c, true, false)) {
+                R = -h;
+                P = 0;
+            }
+            if (in) {
+                if (COPY) out_chunk_off[chunk0 + k] = out_base + P;
+                if (k == m) {
+                    R_last = R;
+                    P_last = P;
+                    have_last = true;
+                }
+            }
+        }
+        {
+            const unsigned who = __ballot_sync(kFull, have_last);
+            const int srcl = who ? __ffs(who) - 1 : 0;
+            R_last = __shfl_sync(kFull, R_last, srcl);
+            P_last = __shfl_sync(kFull, P_last, srcl);
+        }
+        res.total_out = P_last;
+        if (!COPY) return res;
+
+        // ---- 3: bytes and carried state ----
+        if (held_kept && R_last > -h) {
+            if (lane < h) dst[lane] = heldp[lane];
+        }
+        for (int i = 0; i < nruns; i++) {
+            const int rs = __shfl_sync(kFull, run_s, i), rc = __shfl_sync(kFull, run_cum, i);
+            int re = __shfl_sync(kFull, run_e, i);
+            if (has_final && i == nruns - 1 && R_last < re) re = R_last;  // final run: clipped at the release boundary
+            if (re > rs) warp_copy(dst + rc, T.p + rs, re - rs, buf + total, lane);
+        }
+        if (st_out) {
+            int hp = INT32_MIN;  // start of the carried tail (logical coords)
+            if (!(flags & 4u)) {
+                if (depth == 0) {
+                    if (R_last < n) hp = R_last;
+                } else {
+                    int lo = n - kHeldMax;
+                    if (lo < 0) lo = 0;
+                    if (last_tok_end > lo) lo = last_tok_end;
+                    const int x = lo + lane;
+                    const bool islt = x < n && T(x) == '<';
+                    const unsigned bl = __ballot_sync(kFull, islt);
+                    int p = INT32_MIN;
+                    if (bl) p = lo + (31 - __clz(bl));
+                    else if (held_unconsumed && last_tok_end < 0 && n + h <= kHeldMax) p = -h;
+                    if (p != INT32_MIN && is_tag_prefix(tg, A, p, n, false, true)) hp = p;
+                }
+            }
+            if (lane == 0) {
+                StreamState so;
+                so.depth = depth;
+                so.tail_len = last_tok_end >= 0 ? (n - last_tok_end) : -1;
+                so.held_len = 0;
+                for (int i = 0; i < kHeldMax; i++) so.held[i] = 0;
+                if (hp != INT32_MIN) {
+                    so.held_len = (uint8_t)(n - hp);
+                    for (int i = 0; i < so.held_len; i++) so.held[i] = A(hp + i);
+                }
+                *st_out = so;
             }
         }
         return res;

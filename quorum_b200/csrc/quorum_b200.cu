@@ -16,6 +16,7 @@
 #include "../../include/quorum_b200.h"
 #include "qb_walk.cuh"
 #include "qb_tile.cuh"
+#include "qb_tok.cuh"
 #include <stdlib.h>
 
 using namespace qb;
@@ -41,6 +42,41 @@ static int fail(int code, const char* fmt, const char* a = "") {
 #define LAUNCHED() (g_launches.fetch_add(1, std::memory_order_relaxed))
 
 // ---------------------------------------------------------------------------------------------------------------
+// Byte-rescanning walkers, out of line: used when no tokenizer records exist (QB200_PATH=general, the no-alloc entry
+// point) or when a unit touches a step whose record slots overflowed.  Kept out of the record-driven kernels' register
+// budget.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __noinline__ StripResult strip_count_slow(const DevTags& tg, const uint8_t* in, int64_t total, int64_t a, int64_t n,
+                                                     unsigned long long* lc, int lane) {
+    StripWalker<false, false> w(tg, in, total, a, n, lc, lane);
+    w.run();
+    return w.res;
+}
+__device__ __noinline__ void strip_copy_slow(const DevTags& tg, const uint8_t* in, int64_t total, int64_t a, int64_t n,
+                                             unsigned long long* lc, int lane, int64_t first, int64_t kl, uint8_t* dst) {
+    StripWalker<true, false> w(tg, in, total, a, n, lc, lane);
+    w.res.first_pos = first;
+    w.res.kept_len = kl;
+    w.dst = dst;
+    w.run();
+}
+__device__ __noinline__ StreamResult stream_count_slow(const DevTags& tg, const uint8_t* bytes, int64_t total, const int64_t* co,
+                                                       int64_t m, int lane, uint32_t flags, const StreamState* st_in) {
+    StreamWalker<false, false> w(tg, bytes, total, co, m, lane, flags);
+    return w.run(st_in, nullptr);
+}
+__device__ __noinline__ void stream_copy_slow(const DevTags& tg, const uint8_t* bytes, int64_t total, const int64_t* co, int64_t m,
+                                              int lane, uint32_t flags, const StreamState* st_in, StreamState* st_out,
+                                              int64_t base, uint8_t* out, int64_t* out_chunk_off, int64_t c0) {
+    StreamWalker<true, false> w(tg, bytes, total, co, m, lane, flags);
+    w.out_base = base;
+    w.dst = out + base;
+    w.out_chunk_off = out_chunk_off;
+    w.chunk0 = c0;
+    w.run(st_in, st_out);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // kernels: strip + concat
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kWarpsPerBlock = 8;
@@ -49,17 +85,24 @@ constexpr int kThreads = kWarpsPerBlock * 32;
 // scratch layout for strip_concat: int64 klen[n_resp] | int64 first[n_resp] | int64 dst[n_resp] | int64 reqlen[n_req+1]
 __global__ void __launch_bounds__(kThreads)
 strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
-                   int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first) {
+                   int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first, TokSrc ts) {
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
     for (int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib; r < n_resp; r += (int64_t)gridDim.x * kWarpsPerBlock) {
         const int64_t a = in_off[r], b = in_off[r + 1];
-        StripWalker<false> w(tg, in, total, a, b - a, lastclose[wib], lane);
-        w.run();
+        StripResult res;
+        if (ts.cnt && !unit_has_overflow(ts, a, b - a, lane)) {
+            StripWalker<false, true> w(tg, in, total, a, b - a, lastclose[wib], lane);
+            w.ts = ts;
+            w.run();
+            res = w.res;
+        } else {
+            res = strip_count_slow(tg, in, total, a, b - a, lastclose[wib], lane);
+        }
         if (lane == 0) {
-            klen[r] = w.res.kept_len;
-            first[r] = w.res.first_pos;
+            klen[r] = res.kept_len;
+            first[r] = res.first_pos;
         }
         __syncwarp();
     }
@@ -88,42 +131,44 @@ __global__ void request_layout_kernel(const int64_t* __restrict__ in_off, const 
     reqlen[q] = o;
 }
 
-// single-block exclusive scan of v[0..n) into out[0..n], out[n] = total
+// single-block exclusive scan of v[0..n) into out[0..n], out[n] = total.  Warp w owns a contiguous slice and walks it
+// with coalesced 32-wide loads + a shuffle scan; the 32 slice sums are combined once in shared memory.
 __global__ void __launch_bounds__(1024) scan_kernel(const int64_t* __restrict__ v, int64_t n, int64_t* __restrict__ out) {
     __shared__ int64_t warp_excl[32];
-    __shared__ int64_t block_total, carry_s;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (threadIdx.x == 0) carry_s = 0;
+    const int64_t per = ((n + 31) / 32 + 31) / 32 * 32;  // slice length, a multiple of 32
+    const int64_t a = (int64_t)wid * per, b = a + per < n ? a + per : n;
+    int64_t sum = 0;
+    for (int64_t i = a + lane; i < b; i += 32) sum += v[i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(kFull, sum, d);
+    if (lane == 0) warp_excl[wid] = sum;
     __syncthreads();
-    for (int64_t base = 0; base < n; base += 1024) {
-        const int64_t i = base + threadIdx.x;
-        const int64_t x = i < n ? v[i] : 0;
+    if (wid == 0) {
+        const int64_t ws = warp_excl[lane];
+        int64_t wi = ws;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int64_t t = __shfl_up_sync(kFull, wi, d);
+            if (lane >= d) wi += t;
+        }
+        warp_excl[lane] = wi - ws;
+        if (lane == 31) out[n] = wi;
+    }
+    __syncthreads();
+    int64_t run = warp_excl[wid];
+    for (int64_t i0 = a; i0 < b; i0 += 32) {
+        const int64_t i = i0 + lane;
+        const int64_t x = i < b ? v[i] : 0;
         int64_t incl = x;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             int64_t t = __shfl_up_sync(kFull, incl, d);
             if (lane >= d) incl += t;
         }
-        if (lane == 31) warp_excl[wid] = incl;
-        __syncthreads();
-        if (wid == 0) {
-            const int64_t ws = warp_excl[lane];
-            int64_t wi = ws;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                int64_t t = __shfl_up_sync(kFull, wi, d);
-                if (lane >= d) wi += t;
-            }
-            warp_excl[lane] = wi - ws;
-            if (lane == 31) block_total = wi;
-        }
-        __syncthreads();
-        if (i < n) out[i] = carry_s + warp_excl[wid] + incl - x;
-        __syncthreads();
-        if (threadIdx.x == 0) carry_s += block_total;
-        __syncthreads();
+        if (i < b) out[i] = run + incl - x;
+        run += __shfl_sync(kFull, incl, 31);
     }
-    if (threadIdx.x == 0) out[n] = carry_s;
 }
 
 // dst[r] += out_off[request of r]   (thread per request)
@@ -141,7 +186,7 @@ __global__ void __launch_bounds__(kThreads)
 strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
                   int64_t n_resp, const int64_t* __restrict__ klen, const int64_t* __restrict__ first,
                   const int64_t* __restrict__ dst, int hide, const uint8_t* __restrict__ sep, int32_t sep_len,
-                  uint8_t* __restrict__ out, int64_t* __restrict__ resp_out_len) {
+                  uint8_t* __restrict__ out, int64_t* __restrict__ resp_out_len, TokSrc ts) {
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
@@ -157,11 +202,18 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
         const int64_t kl = hide ? klen[r] : (b - a);
         if (resp_out_len && lane == 0) resp_out_len[r] = kl;
         if (hide) {
-            StripWalker<true> w(tg, in, total, a, b - a, lastclose[wib], lane);
-            w.res.first_pos = first[r];
-            w.res.kept_len = kl;
-            w.dst = out + d;
-            if (kl > 0) w.run();
+            if (kl > 0) {
+                if (ts.cnt && !unit_has_overflow(ts, a, b - a, lane)) {
+                    StripWalker<true, true> w(tg, in, total, a, b - a, lastclose[wib], lane);
+                    w.ts = ts;
+                    w.res.first_pos = first[r];
+                    w.res.kept_len = kl;
+                    w.dst = out + d;
+                    w.run();
+                } else {
+                    strip_copy_slow(tg, in, total, a, b - a, lastclose[wib], lane, first[r], kl, out + d);
+                }
+            }
         } else {
             warp_copy(out + d, in + a, b - a, in + total, lane);
         }
@@ -187,40 +239,54 @@ __global__ void separator_kernel(const int64_t* __restrict__ req_off, int64_t n_
 // ---------------------------------------------------------------------------------------------------------------
 // kernels: stream feed
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 3)
 stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                     const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                     int64_t n_streams, const StreamState* __restrict__ st_in, uint32_t flags,
-                    int64_t* __restrict__ totals) {
+                    int64_t* __restrict__ totals, TokSrc ts) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
     for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
         const int64_t c0 = stream_off[s], c1 = stream_off[s + 1];
-        StreamWalker<false> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags);
-        StreamResult r = w.run(st_in ? st_in + s : nullptr, nullptr);
+        StreamResult r;
+        bool slow = ts.cnt == nullptr;
+        if (!slow) {
+            StreamRunWalker<false> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
+            r = w.run(st_in ? st_in + s : nullptr, nullptr);
+            slow = w.overflow;  // a step ran out of record slots: redo this unit from its bytes
+        }
+        if (slow) r = stream_count_slow(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, st_in ? st_in + s : nullptr);
         if (lane == 0) totals[s] = r.total_out;
         __syncwarp();
     }
 }
 
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 3)
 stream_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                    const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                    int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
-                   const int64_t* __restrict__ bases, uint8_t* __restrict__ out, int64_t* __restrict__ out_chunk_off) {
+                   const int64_t* __restrict__ bases, uint8_t* __restrict__ out, int64_t* __restrict__ out_chunk_off,
+                   TokSrc ts) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
     for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
         const int64_t c0 = stream_off[s], c1 = stream_off[s + 1];
-        StreamWalker<true> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags);
-        w.out_base = bases[s];
-        w.dst = out + bases[s];
-        w.out_chunk_off = out_chunk_off;
-        w.chunk0 = c0;
         // state_in may alias state_out: the walker reads its input state before writing the output state
         StreamState si;
         if (st_in) si = st_in[s];
-        w.run(st_in ? &si : nullptr, st_out ? st_out + s : nullptr);
+        bool slow = ts.cnt == nullptr;
+        if (!slow) {
+            StreamRunWalker<true> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
+            w.out_base = bases[s];
+            w.dst = out + bases[s];
+            w.out_chunk_off = out_chunk_off;
+            w.chunk0 = c0;
+            w.run(st_in ? &si : nullptr, st_out ? st_out + s : nullptr);
+            slow = w.overflow;  // rewritten below from the bytes: same base, same offsets
+        }
+        if (slow)
+            stream_copy_slow(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, st_in ? &si : nullptr,
+                             st_out ? st_out + s : nullptr, bases[s], out, out_chunk_off, c0);
         __syncwarp();
     }
     if (blockIdx.x == 0 && threadIdx.x == 0 && n_streams == 0) out_chunk_off[0] = 0;
@@ -323,10 +389,47 @@ void qb200_tags_destroy(qb200_tags* tags) { delete tags; }
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req) {
+// QB200_PATH selects the implementation (default "token"): "token" = tokenizer pass + record-driven walkers,
+// "tile" = fused single-pass tile kernel (streams only), "general" = walkers that rescan the bytes.
+static int path_choice() {
+    const char* e = getenv("QB200_PATH");
+    if (e && strcmp(e, "general") == 0) return 0;
+    if (e && strcmp(e, "tile") == 0) return 1;
+    return 2;
+}
+
+static int64_t steps_for(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte_bound) / 1024 + 2; }
+static size_t tok_scratch_bytes(int64_t byte_bound) {
+    const int64_t st = steps_for(byte_bound);
+    return align256((size_t)st) + align256((size_t)st * kRecPerStep * 4) + 256;
+}
+
+// tokenizer pass over the flat buffer; returns where the records are
+static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const int64_t* total_ptr, int64_t byte_bound,
+                               uint8_t* scratch, cudaStream_t stream) {
+    const int64_t st = steps_for(byte_bound);
+    TokSrc ts;
+    uint8_t* cnt = scratch;
+    uint32_t* rec = (uint32_t*)(scratch + align256((size_t)st));
+    int64_t blocks = (st + 7) / 8;
+    const int64_t cap = 148 * 8 * 4;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    tokenize_kernel<<<(unsigned)blocks, 256, 0, stream>>>(tg, bytes, total_ptr, cnt, rec, st);
+    LAUNCHED();
+    ts.cnt = cnt;
+    ts.rec = rec;
+    return ts;
+}
+
+static size_t strip_general_scratch_bytes(int64_t n_resp, int64_t n_req) {
     if (n_resp < 0) n_resp = 0;
     if (n_req < 0) n_req = 0;
     return 3 * align256((size_t)(n_resp + 1) * 8) + align256((size_t)(n_req + 2) * 8) + 256;
+}
+
+size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req, int64_t out_capacity) {
+    return strip_general_scratch_bytes(n_resp, n_req) + tok_scratch_bytes(out_capacity) + 256;
 }
 
 static int grid_for(int64_t units) {
@@ -348,8 +451,8 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     if (out_capacity < 0) return fail(QB200_EINVAL, "strip_concat_batch: negative out_capacity");
     if (((uintptr_t)in_bytes & 15) || ((uintptr_t)out_bytes & 15))
         return fail(QB200_EINVAL, "strip_concat_batch: in_bytes/out_bytes must be 16-byte aligned");
-    if (scratch_bytes < qb200_strip_concat_scratch_bytes(n_resp, n_req) || !scratch)
-        return fail(QB200_ESCRATCH, "strip_concat_batch: scratch too small");
+    if (scratch_bytes < qb200_strip_concat_scratch_bytes(n_resp, n_req, out_capacity) || !scratch)
+        return fail(QB200_ESCRATCH, "strip_concat_batch: scratch too small (see qb200_strip_concat_scratch_bytes)");
     int dev_count = 0;
     CUDA_TRY(cudaGetDeviceCount(&dev_count));
     if (n_req == 0) {
@@ -369,8 +472,12 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     const int hide = (flags & QB200_HIDE) ? 1 : 0;
     const int sj = (flags & QB200_STREAM_JOIN) ? 1 : 0;
 
+    TokSrc ts;
+    if (hide && n_resp > 0 && path_choice() != 0)
+        ts = launch_tokenizer(tags->dev, in_bytes, in_off + n_resp, out_capacity,
+                              (uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req), stream);
     if (hide && n_resp > 0) {
-        strip_count_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first);
+        strip_count_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts);
         LAUNCHED();
     }
     const int tb = 256;
@@ -383,7 +490,7 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     LAUNCHED();
     if (n_resp > 0) {
         strip_copy_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, dst,
-                                                                    hide, sep, sep_len, out_bytes, resp_out_len);
+                                                                    hide, sep, sep_len, out_bytes, resp_out_len, ts);
         LAUNCHED();
     }
     if (sep_len > 0 && req_off) {
@@ -406,12 +513,8 @@ static size_t tile_scratch_bytes(int64_t max_tiles) { return align256((size_t)(m
 
 size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity) {
     (void)n_chunks;
-    return stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity)) + 256;
-}
-
-static bool force_general() {
-    const char* e = getenv("QB200_PATH");
-    return e && strcmp(e, "general") == 0;
+    return stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity)) +
+           tok_scratch_bytes(out_capacity) + 256;
 }
 
 static int stream_feed_check(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
@@ -430,7 +533,8 @@ static int stream_feed_check(const qb200_tags* tags, const uint8_t* chunk_bytes,
 static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
                                const int64_t* stream_off, int64_t n_streams, const qb200_stream_state* state_in,
                                qb200_stream_state* state_out, uint32_t flags, uint8_t* out_bytes, int64_t out_capacity,
-                               int64_t* out_chunk_off, void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+                               int64_t* out_chunk_off, void* scratch, size_t scratch_bytes, cudaStream_t stream,
+                               bool use_tokens = false) {
     int rc = stream_feed_check(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, out_bytes, out_capacity,
                                out_chunk_off);
     if (rc != QB200_OK) return rc;
@@ -448,13 +552,18 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     int64_t* bases = (int64_t*)sp;
     const StreamState* si = reinterpret_cast<const StreamState*>(state_in);
     StreamState* so = reinterpret_cast<StreamState*>(state_out);
+    TokSrc ts;
+    if (use_tokens) {  // records live behind the general + tile scratch regions (see qb200_stream_feed_scratch_bytes)
+        uint8_t* tsp = (uint8_t*)scratch + stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity));
+        ts = launch_tokenizer(tags->dev, chunk_bytes, chunk_off + n_chunks, out_capacity, tsp, stream);
+    }
     stream_count_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
-                                                                     n_streams, si, flags, totals);
+                                                                     n_streams, si, flags, totals, ts);
     LAUNCHED();
     scan_kernel<<<1, 1024, 0, stream>>>(totals, n_streams, bases);
     LAUNCHED();
     stream_copy_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
-                                                                    n_streams, si, so, flags, bases, out_bytes, out_chunk_off);
+                                                                    n_streams, si, so, flags, bases, out_bytes, out_chunk_off, ts);
     LAUNCHED();
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
@@ -475,9 +584,14 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
                             qb200_stream_state* state_out, uint32_t flags, uint8_t* out_bytes, int64_t out_capacity,
                             int64_t* out_chunk_off, void* scratch, size_t scratch_bytes, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
-    if (force_general() || n_streams == 0)
+    const int path = path_choice();
+    if (path != 1 || n_streams == 0) {
+        const bool tok = path == 2 && n_streams > 0;
+        if (tok && (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams, out_capacity) || !scratch))
+            return fail(QB200_ESCRATCH, "stream_feed_batch: scratch too small (see qb200_stream_feed_scratch_bytes)");
         return stream_feed_general(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, state_in, state_out, flags,
-                                   out_bytes, out_capacity, out_chunk_off, scratch, scratch_bytes, stream);
+                                   out_bytes, out_capacity, out_chunk_off, scratch, scratch_bytes, stream, tok);
+    }
     int rc = stream_feed_check(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, out_bytes, out_capacity,
                                out_chunk_off);
     if (rc != QB200_OK) return rc;

@@ -248,6 +248,15 @@ __device__ __forceinline__ uint32_t lt_nibble(uint32_t w) {
     return (t * 0x00204081u) >> 28;    // gather bits 7,15,23,31 -> 0..3
 }
 
+// non-zero iff some byte of w equals '<' (exact as a boolean; the borrow only smears above a real hit)
+__device__ __forceinline__ uint32_t lt_any(uint32_t w) {
+    const uint32_t v = w ^ 0x3C3C3C3Cu;
+    return (v - 0x01010101u) & ~v & 0x80808080u;
+}
+__device__ __forceinline__ uint32_t lt_any32(const uint4& a, const uint4& b) {
+    return lt_any(a.x) | lt_any(a.y) | lt_any(a.z) | lt_any(a.w) | lt_any(b.x) | lt_any(b.y) | lt_any(b.z) | lt_any(b.w);
+}
+
 __device__ __forceinline__ uint32_t lt_mask16(uint4 v) {
     return lt_nibble(v.x) | (lt_nibble(v.y) << 4) | (lt_nibble(v.z) << 8) | (lt_nibble(v.w) << 12);
 }
@@ -295,30 +304,41 @@ __device__ inline void warp_copy(uint8_t* dst, const uint8_t* src, int64_t n, co
     }
     uint4* d4 = reinterpret_cast<uint4*>(dst);
     const int wsel = shift >> 2, sh = (shift & 3) * 8;
-    if (PREFETCH && nvec > 32) {  // more than one round of loads: get every line moving before the first store waits
-        const uint8_t* base = reinterpret_cast<const uint8_t*>(s128);
-        const int64_t bytes = (nvec + 1) << 4;
-        for (int64_t o = (int64_t)lane * 128; o < bytes; o += 32 * 128)
-            asm volatile("prefetch.L1 [%0];" ::"l"(base + o));  // generic address: a no-op for shared memory
-    }
-    for (int64_t v = lane; v < nvec; v += 32) {
-        const uint4 A = s128[v];
-        uint4 o = A;
-        if (shift) {
-            const uint4 B = s128[v + 1];
-            uint32_t w0, w1, w2, w3, w4;
-            switch (wsel) {
-                case 0: w0 = A.x; w1 = A.y; w2 = A.z; w3 = A.w; w4 = B.x; break;
-                case 1: w0 = A.y; w1 = A.z; w2 = A.w; w3 = B.x; w4 = B.y; break;
-                case 2: w0 = A.z; w1 = A.w; w2 = B.x; w3 = B.y; w4 = B.z; break;
-                default: w0 = A.w; w1 = B.x; w2 = B.y; w3 = B.z; w4 = B.w; break;
-            }
-            o.x = __funnelshift_r(w0, w1, sh);
-            o.y = __funnelshift_r(w1, w2, sh);
-            o.z = __funnelshift_r(w2, w3, sh);
-            o.w = __funnelshift_r(w3, w4, sh);
+    auto realign = [&](const uint4& A, const uint4& B) -> uint4 {
+        uint32_t w0, w1, w2, w3, w4;
+        switch (wsel) {
+            case 0: w0 = A.x; w1 = A.y; w2 = A.z; w3 = A.w; w4 = B.x; break;
+            case 1: w0 = A.y; w1 = A.z; w2 = A.w; w3 = B.x; w4 = B.y; break;
+            case 2: w0 = A.z; w1 = A.w; w2 = B.x; w3 = B.y; w4 = B.z; break;
+            default: w0 = A.w; w1 = B.x; w2 = B.y; w3 = B.z; w4 = B.w; break;
         }
-        d4[v] = o;
+        uint4 o;
+        o.x = __funnelshift_r(w0, w1, sh);
+        o.y = __funnelshift_r(w1, w2, sh);
+        o.z = __funnelshift_r(w2, w3, sh);
+        o.w = __funnelshift_r(w3, w4, sh);
+        return o;
+    };
+    int64_t v = lane;
+    if (shift == 0) {
+        for (; v + 96 < nvec; v += 128) {  // four independent rounds in flight
+            const uint4 a0 = s128[v], a1 = s128[v + 32], a2 = s128[v + 64], a3 = s128[v + 96];
+            d4[v] = a0;
+            d4[v + 32] = a1;
+            d4[v + 64] = a2;
+            d4[v + 96] = a3;
+        }
+        for (; v < nvec; v += 32) d4[v] = s128[v];
+    } else {
+        for (; v + 32 < nvec; v += 64) {  // two rounds (four loads) in flight before the first store waits
+            const uint4 a0 = s128[v], b0 = s128[v + 1], a1 = s128[v + 32], b1 = s128[v + 33];
+            d4[v] = realign(a0, b0);
+            d4[v + 32] = realign(a1, b1);
+        }
+        for (; v < nvec; v += 32) {
+            const uint4 a0 = s128[v], b0 = s128[v + 1];
+            d4[v] = realign(a0, b0);
+        }
     }
     for (int64_t i = (nvec << 4) + lane; i < n; i += 32) dst[i] = src[i];
 }

@@ -47,10 +47,15 @@ __global__ void __launch_bounds__(256) tokenize_kernel(const __grid_constant__ D
         if (a + 32 <= total) {
             const uint4* p = reinterpret_cast<const uint4*>(bytes + a);
             const uint4 lo = __ldcs(p), hi = __ldcs(p + 1);  // streamed: every byte is read exactly once by this pass
-            lt = lt_mask16(lo) | (lt_mask16(hi) << 16);
+            if (lt_any32(lo, hi)) lt = lt_mask16(lo) | (lt_mask16(hi) << 16);  // exact positions only where needed
         } else {
             for (int b = 0; b < 32 && a + b < total; b++)
                 if (bytes[a + b] == '<') lt |= 1u << b;
+        }
+        const unsigned any = __ballot_sync(kFull, lt != 0);
+        if (any == 0) {  // the common case: no '<' in this KiB
+            if (lane == 0) cnt[step] = 0;
+            continue;
         }
         // records of this lane's word (a 32-byte word holds at most 10 three-byte tags; more than 4 '<' is an overflow)
         uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0;
@@ -70,13 +75,19 @@ __global__ void __launch_bounds__(256) tokenize_kernel(const __grid_constant__ D
             else many = true;
             n++;
         }
-        int incl = n;
+        int incl, tot;
+        if (__all_sync(kFull, n <= 1)) {  // one record per lane at most: ranks straight from the ballot
+            incl = __popc(any & (0xffffffffu >> (31 - lane)));
+            tot = __popc(any);
+        } else {
+            incl = n;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int t = __shfl_up_sync(kFull, incl, d);
-            if (lane >= d) incl += t;
+            for (int d = 1; d < 32; d <<= 1) {
+                int t = __shfl_up_sync(kFull, incl, d);
+                if (lane >= d) incl += t;
+            }
+            tot = __shfl_sync(kFull, incl, 31);
         }
-        const int tot = __shfl_sync(kFull, incl, 31);
         const bool bad = __any_sync(kFull, many) || tot > kRecPerStep;
         if (!bad && n > 0) {
             uint32_t* out = rec + step * kRecPerStep + (incl - n);

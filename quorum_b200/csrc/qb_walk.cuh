@@ -829,10 +829,13 @@ struct StreamRunWalker {
         int R_last = 0, P_last = 0;
         bool have_last = false;
         if (COPY && lane == 0) out_chunk_off[chunk0] = out_base;
-        for (int64_t kb = COPY ? 1 : m; kb <= m; kb += 32) {
+        const int64_t kb0 = COPY ? 1 : m;
+        int64_t cnext = kb0 + lane <= m ? co[kb0 + lane] : 0;  // boundaries are fetched one batch ahead
+        for (int64_t kb = kb0; kb <= m; kb += 32) {
             const int64_t k = kb + lane;
             const bool in = k <= m;
-            const int c = in ? (int)(co[k] - ustart) : 0;
+            const int c = in ? (int)(cnext - ustart) : 0;
+            if (k + 32 <= m) cnext = co[k + 32];
             // last '<' in [c - kHeldMax, c): look through the records of the step that holds byte c-1 and, when the
             // window reaches back into it, of the step before (per lane, no warp-wide operation in here)
             int p = -1;

@@ -33,6 +33,16 @@ __device__ __forceinline__ uint32_t rec_select(const uint4& a, const uint4& b, i
         default: return b.w;
     }
 }
+// What the walk of one unit leaves behind for the kernels that follow (per-chunk offsets, gather copy): the kept runs of
+// the unit in unit coordinates plus the few scalars of the automaton's final state.  nruns < 0: the unit did not fit
+// (more than kDescRuns runs, overflowed record slots, 2 GiB and more) and is redone by the byte-rescanning walkers.
+constexpr int kDescRuns = 8;
+struct UnitDesc {
+    int32_t nruns, total, held_kept, depth, last_tok_end, rlast, flags, pad;  // flags: 1 held '<' unconsumed, 2 final run open-ended
+    int32_t run_s[kDescRuns], run_e[kDescRuns];
+};
+static_assert(sizeof(UnitDesc) == 96, "descriptor layout");
+
 // true when any step touched by the unit [ustart, ustart+n) overflowed its record slots (then the unit is walked
 // the slow way, straight from its bytes)
 __device__ inline bool unit_has_overflow(const TokSrc& ts, int64_t ustart, int64_t n, int lane) {
@@ -56,7 +66,7 @@ struct StripResult {
     int64_t kept_len;   // output length after filter + strip
 };
 
-template <bool COPY, bool TOK = false>
+template <bool COPY>
 struct StripWalker {
     const DevTags& tg;
     const uint8_t* buf;   // flat buffer base (16-byte aligned)
@@ -71,7 +81,6 @@ struct StripWalker {
     StripResult res{0, 0};
     // copy pass
     uint8_t* dst = nullptr;
-    TokSrc ts;  // when set: tags come from the tokenizer's records instead of rescanning the bytes
 
     __device__ StripWalker(const DevTags& tg_, const uint8_t* buf_, int64_t total_, int64_t ustart_, int64_t n_,
                            unsigned long long* lc, int lane_)
@@ -146,63 +155,8 @@ struct StripWalker {
         }
     }
 
-    // Token mode: lane j holds the records of step S0 + j of the current group of 32 steps.
-    __device__ void run_tokens() {
-        const int64_t s_first = ustart >> 10, s_last = (ustart + n - 1) >> 10;
-        for (int c = lane; c < tg.ncls; c += 32) lastclose[c] = 0;
-        __syncwarp();
-        for (int pass = 0; pass < 2; pass++) {
-            for (int64_t S0 = s_first; S0 <= s_last; S0 += 32) {
-                const int64_t sj = S0 + lane;
-                int cnt = 0;
-                uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
-                if (sj <= s_last) {
-                    cnt = ts.cnt[sj];
-                    if (cnt > 0) {
-                        const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);
-                        ra = rp[0];
-                        if (cnt > 4) rb = rp[1];
-                    }
-                }
-                if (pass == 0) {  // pass A: last closer per class, every lane over its own step
-                    for (int k = 0; k < cnt; k++) {
-                        const uint32_t r = rec_select(ra, rb, k);
-                        if (((r >> 17) & 3) != 1) continue;
-                        const int64_t x = (sj << 10) + (r & 1023) - ustart;
-                        const int64_t tend = x + ((r >> 10) & 127);
-                        if (x >= 0 && tend <= n) atomicMax(&lastclose[(r >> 19) & 127], (unsigned long long)(x + 1));
-                    }
-                } else {  // pass B: tokens in position order
-                    unsigned live = __ballot_sync(kFull, cnt > 0);
-                    while (live) {
-                        const int j = __ffs(live) - 1;
-                        live &= live - 1;
-                        const int c = __shfl_sync(kFull, cnt, j);
-#pragma unroll
-                        for (int k = 0; k < kRecPerStep; k++) {
-                            if (k >= c) break;
-                            const uint32_t r = __shfl_sync(kFull, rec_select(ra, rb, k), j);
-                            const int kind = (r >> 17) & 3;
-                            if (kind == 2) continue;
-                            const int64_t x = ((S0 + j) << 10) + (r & 1023) - ustart;
-                            const int64_t tend = x + ((r >> 10) & 127);
-                            if (x < 0 || tend > n) continue;
-                            event(x, tend, (r >> 19) & 127, kind == 1);
-                        }
-                    }
-                }
-            }
-            __syncwarp();
-        }
-        emit(seg_start, n);
-    }
-
     __device__ void run() {
         if (n <= 0) return;
-        if (TOK) {
-            run_tokens();
-            return;
-        }
         const int64_t w_first = ustart >> 5, w_last = (ustart + n - 1) >> 5;
         const int64_t nsteps = (w_last - w_first + 32) >> 5;
         for (int c = lane; c < tg.ncls; c += 32) lastclose[c] = 0;
@@ -278,7 +232,7 @@ struct StreamResult {
     int64_t total_out;  // kept bytes released by this call
 };
 
-template <bool COPY, bool TOK = false>
+template <bool COPY>
 struct StreamWalker {
     const DevTags& tg;
     const uint8_t* buf;
@@ -292,8 +246,6 @@ struct StreamWalker {
     int64_t out_base = 0;            // absolute output offset of this stream
     int64_t* out_chunk_off = nullptr;  // global array, indexed by absolute chunk index
     int64_t chunk0 = 0;              // absolute index of this stream's first chunk
-    TokSrc ts;                       // when set: tags come from the tokenizer's records instead of rescanning the bytes
-    bool overflow = false;           // token mode: a step of this unit had more '<' than record slots (result invalid)
 
     __device__ StreamWalker(const DevTags& tg_, const uint8_t* buf_, int64_t total_, const int64_t* co_, int64_t m_,
                             int lane_, uint32_t flags_)
@@ -386,12 +338,9 @@ struct StreamWalker {
         const int64_t w_first = (ustart >> 10) << 5;  // steps sit on the absolute 1 KiB grid (the tokenizer's grid)
         const int64_t w_last = n > 0 ? ((ustart + n - 1) >> 5) : (w_first - 1);
         const int64_t nsteps = n > 0 ? ((w_last - w_first + 32) >> 5) : 1;  // one (empty) step accounts empty chunks
-        constexpr bool tokmode = TOK;
         // feed boundaries are fetched one step ahead: cpre = co[pre_base + lane]
         int64_t pre_base = kb;
         int64_t cpre = (kb + lane <= m) ? co[kb + lane] - ustart : INT64_MAX;
-        int g_cnt = 0;  // token mode: this lane's records of step (group start + lane)
-        uint4 g_ra = make_uint4(0, 0, 0, 0), g_rb = g_ra;
         for (int64_t s = 0; s < nsteps; s++) {
             const int64_t w = w_first + s * 32 + lane;
             const int64_t wb = (w << 5) - ustart;
@@ -418,45 +367,7 @@ struct StreamWalker {
                 }
                 last_tok_end = skip_until = tend;
             };
-            if (tokmode) {
-                if ((s & 31) == 0) {  // fetch the records of the next 32 steps, one step per lane
-                    const int64_t sj = (w_first >> 5) + s + lane;
-                    g_cnt = 0;
-                    if (n > 0 && sj <= ((ustart + n - 1) >> 10)) {
-                        g_cnt = ts.cnt[sj];
-                        if (g_cnt == kRecOverflow) g_cnt = -1;
-                        if (g_cnt > 0) {
-                            const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);
-                            g_ra = rp[0];
-                            if (g_cnt > 4) g_rb = rp[1];
-                        }
-                    }
-                    if (__any_sync(kFull, g_cnt < 0)) {  // stop before anything derived from missing records is written
-                        overflow = true;
-                        return res;
-                    }
-                }
-                const int j = (int)(s & 31);
-                const int c = __shfl_sync(kFull, g_cnt, j);
-#pragma unroll
-                for (int k = 0; k < kRecPerStep; k++) {
-                    if (k >= c) break;
-                    const uint32_t r = __shfl_sync(kFull, rec_select(g_ra, g_rb, k), j);
-                    const int pos = (int)(r & 1023);
-                    const int64_t x = ((w_first + s * 32) << 5) + pos - ustart;
-                    if (x < 0 || x >= n) continue;
-                    if (lane == (pos >> 5)) lt |= 1u << (pos & 31);
-                    const int kind = (r >> 17) & 3;
-                    const int64_t tend = x + ((r >> 10) & 127);
-                    if (kind == 2 || tend > n || x < skip_until) continue;  // literal '<', or a tag cut by the unit end
-                    int64_t ex = -1;
-                    if (((r >> 26) & 1) && depth == 0 && kind == 0) {  // rare: which letter uses a non-ASCII form?
-                        int cls;
-                        match_tag(tg, T, x, n, false, cls, ex);
-                    }
-                    on_tag(x, tend, kind == 1, ex);
-                }
-            } else {
+            {
                 lt = (w <= w_last) ? (load_lt_word(buf, total, w) & range) : 0u;
                 uint32_t tok = 0;
                 {
@@ -647,8 +558,10 @@ struct StreamWalker {
 // The count pass is phase 1 plus the last boundary.  Positions are unit-relative int32 (units of 2 GiB and more take
 // the fallback).
 // ------------------------------------------------------------------------------------------------------------------
-template <bool COPY>
+template <int MODE>  // 0: walk + released total + descriptor;  1: per-chunk offsets + carried state from a descriptor
 struct StreamRunWalker {
+    static constexpr bool COPY = MODE == 1;
+    UnitDesc* desc = nullptr;
     const DevTags& tg;
     const uint8_t* buf;
     int64_t total;
@@ -729,12 +642,6 @@ struct StreamRunWalker {
                     run_e = e;
                     run_cum = cum;
                 }
-                if (COPY) {  // get the run's source lines moving; they are copied after the boundary work
-                    const uint8_t* a = T.p + seg_start;
-                    const uint8_t* base = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(a) & ~(uintptr_t)127);
-                    const int64_t bytes = (a - base) + (e - seg_start);
-                    for (int64_t o = (int64_t)lane * 128; o < bytes; o += 32 * 128) asm volatile("prefetch.L2 [%0];" ::"l"(base + o));
-                }
                 nruns++;
                 cum += e - seg_start;
             }
@@ -751,78 +658,93 @@ struct StreamRunWalker {
             last_tok_end = tend;
         };
 
-        // ---- the carried partial tag (positions -h .. -1) ----
-        if (h > 0) {
-            int cls;
-            int64_t ex;
-            int64_t tend = match_tag(tg, A, -h, n, false, cls, ex);
-            bool is_close = false;
-            if (tend < 0 && depth > 0) {
-                tend = match_tag(tg, A, -h, n, true, cls, ex);
-                is_close = true;
+        bool has_final = false;
+        if (MODE == 1) {  // everything phase 1 would find out is in the descriptor
+            const UnitDesc& d = *desc;
+            nruns = d.nruns;
+            held_kept = (d.flags & 4) ? h : 0;
+            depth = d.depth;
+            last_tok_end = d.last_tok_end;
+            held_unconsumed = (d.flags & 1) != 0;
+            has_final = (d.flags & 2) != 0;
+            if (lane < kDescRuns) {
+                run_s = d.run_s[lane];
+                run_e = d.run_e[lane];
             }
-            if (tend >= 0 && recognised(is_close, -h, (int)tend, (int)ex)) {
-                depth += is_close ? -1 : 1;
-                last_tok_end = seg_start = (int)tend;
-            } else {
-                held_unconsumed = true;
-                if (depth == 0) held_kept = h;
+        } else {
+            // ---- the carried partial tag (positions -h .. -1) ----
+            if (h > 0) {
+                int cls;
+                int64_t ex;
+                int64_t tend = match_tag(tg, A, -h, n, false, cls, ex);
+                bool is_close = false;
+                if (tend < 0 && depth > 0) {
+                    tend = match_tag(tg, A, -h, n, true, cls, ex);
+                    is_close = true;
+                }
+                if (tend >= 0 && recognised(is_close, -h, (int)tend, (int)ex)) {
+                    depth += is_close ? -1 : 1;
+                    last_tok_end = seg_start = (int)tend;
+                } else {
+                    held_unconsumed = true;
+                    if (depth == 0) held_kept = h;
+                }
             }
-        }
-        cum = held_kept;
+            cum = held_kept;
 
-        // ---- 1: token records of the unit, steps with records only ----
-        if (n > 0) {
-            const int64_t s_first = ustart >> 10, s_last = (ustart + n - 1) >> 10;
-            for (int64_t S0 = s_first; S0 <= s_last; S0 += 32) {
-                const int64_t sj = S0 + lane;
-                int cnt = 0;
-                uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
-                if (sj <= s_last) {
-                    cnt = ts.cnt[sj];
-                    if (cnt == kRecOverflow) cnt = -1;
-                    if (cnt > 0) {
-                        const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);
-                        ra = rp[0];
-                        if (cnt > 4) rb = rp[1];
-                    }
-                }
-                if (__any_sync(kFull, cnt < 0)) {
-                    overflow = true;
-                    return res;
-                }
-                unsigned live = __ballot_sync(kFull, cnt > 0);
-                while (live) {
-                    const int j = __ffs(live) - 1;
-                    live &= live - 1;
-                    const int c = __shfl_sync(kFull, cnt, j);
-                    const int sb = (int)(((S0 + j) << 10) - ustart);  // unit position of the step's first byte
-#pragma unroll
-                    for (int k = 0; k < kRecPerStep; k++) {
-                        if (k >= c) break;
-                        const uint32_t r = __shfl_sync(kFull, rec_select(ra, rb, k), j);
-                        const int kind = (r >> 17) & 3;
-                        const int x = sb + (int)(r & 1023);
-                        const int tend = x + (int)((r >> 10) & 127);
-                        if (kind == 2 || x < 0 || tend > n || x < last_tok_end) continue;  // literal '<' / cut by the unit
-                        int ex = -1;
-                        if (((r >> 26) & 1) && depth == 0 && kind == 0) {  // rare: which letter uses a non-ASCII form?
-                            int cls;
-                            int64_t e64;
-                            match_tag(tg, T, x, n, false, cls, e64);
-                            ex = (int)e64;
+            // ---- 1: token records of the unit, steps with records only ----
+            if (n > 0) {
+                const int64_t s_first = ustart >> 10, s_last = (ustart + n - 1) >> 10;
+                for (int64_t S0 = s_first; S0 <= s_last; S0 += 32) {
+                    const int64_t sj = S0 + lane;
+                    int cnt = 0;
+                    uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
+                    if (sj <= s_last) {
+                        cnt = ts.cnt[sj];
+                        if (cnt == kRecOverflow) cnt = -1;
+                        if (cnt > 0) {
+                            const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);
+                            ra = rp[0];
+                            if (cnt > 4) rb = rp[1];
                         }
-                        on_tag(x, tend, kind == 1, ex);
+                    }
+                    if (__any_sync(kFull, cnt < 0)) {
+                        overflow = true;
+                        return res;
+                    }
+                    unsigned live = __ballot_sync(kFull, cnt > 0);
+                    while (live) {
+                        const int j = __ffs(live) - 1;
+                        live &= live - 1;
+                        const int c = __shfl_sync(kFull, cnt, j);
+                        const int sb = (int)(((S0 + j) << 10) - ustart);  // unit position of the step's first byte
+    #pragma unroll
+                        for (int k = 0; k < kRecPerStep; k++) {
+                            if (k >= c) break;
+                            const uint32_t r = __shfl_sync(kFull, rec_select(ra, rb, k), j);
+                            const int kind = (r >> 17) & 3;
+                            const int x = sb + (int)(r & 1023);
+                            const int tend = x + (int)((r >> 10) & 127);
+                            if (kind == 2 || x < 0 || tend > n || x < last_tok_end) continue;  // literal '<' / cut by the unit
+                            int ex = -1;
+                            if (((r >> 26) & 1) && depth == 0 && kind == 0) {  // rare: which letter uses a non-ASCII form?
+                                int cls;
+                                int64_t e64;
+                                match_tag(tg, T, x, n, false, cls, e64);
+                                ex = (int)e64;
+                            }
+                            on_tag(x, tend, kind == 1, ex);
+                        }
                     }
                 }
             }
-        }
-        const int nclosed = nruns;       // runs ended by an open tag
-        if (depth == 0) close_run(n);    // the final run, clipped later at the last release boundary
-        const bool has_final = nruns > nclosed;
-        if (nruns > 32) {
-            overflow = true;
-            return res;
+            const int nclosed = nruns;       // runs ended by an open tag
+            if (depth == 0) close_run(n);    // the final run, clipped later at the last release boundary
+            has_final = nruns > nclosed;
+            if (nruns > kDescRuns) {
+                overflow = true;
+                return res;
+            }
         }
 
         // ---- 2: feed boundaries, one per lane ----
@@ -894,17 +816,30 @@ struct StreamRunWalker {
             P_last = __shfl_sync(kFull, P_last, srcl);
         }
         res.total_out = P_last;
-        if (!COPY) return res;
+        if (MODE == 0) {
+            if (desc) {
+                UnitDesc& d = *desc;
+                if (lane == 0) {
+                    d.nruns = nruns;
+                    d.total = P_last;
+                    d.held_kept = (held_kept && R_last > -h) ? held_kept : 0;  // carried literal bytes that are released
+                    d.depth = depth;
+                    d.last_tok_end = last_tok_end;
+                    d.rlast = R_last;
+                    d.flags = (held_unconsumed ? 1 : 0) | (has_final ? 2 : 0) | (held_kept ? 4 : 0);
+                    d.pad = 0;
+                }
+                if (lane < kDescRuns) {  // unclipped; the copy clips the open-ended final run at rlast
+                    d.run_s[lane] = lane < nruns ? run_s : 0;
+                    d.run_e[lane] = lane < nruns ? run_e : 0;
+                }
+            }
+            return res;
+        }
 
-        // ---- 3: bytes and carried state ----
+        // ---- 3: carried literal bytes and carried state (the kept runs are copied by the gather kernel) ----
         if (held_kept && R_last > -h) {
             if (lane < h) dst[lane] = heldp[lane];
-        }
-        for (int i = 0; i < nruns; i++) {
-            const int rs = __shfl_sync(kFull, run_s, i), rc = __shfl_sync(kFull, run_cum, i);
-            int re = __shfl_sync(kFull, run_e, i);
-            if (has_final && i == nruns - 1 && R_last < re) re = R_last;  // final run: clipped at the release boundary
-            if (re > rs) warp_copy(dst + rc, T.p + rs, re - rs, buf + total, lane);
         }
         if (st_out) {
             int hp = INT32_MIN;  // start of the carried tail (logical coords)
@@ -938,6 +873,185 @@ struct StreamRunWalker {
             }
         }
         return res;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------------------------
+// Record-driven strip walker ("run list"): the fast path of strip_thinking_tags.
+//
+// Same semantics as StripWalker.  The warp reads the unit's token records once (one step per lane), records the last
+// closer of every class (pass A, lanes in parallel), walks the tags in position order (pass B) and keeps the kept runs
+// of the response one per lane.  `.strip()` then only has to look at the two ends of that list.  More than 32 runs, a
+// step whose records overflowed, or a response of 2 GiB and more set `overflow` (the caller falls back to StripWalker).
+// ------------------------------------------------------------------------------------------------------------------
+template <bool COPY>
+struct StripRunWalker {
+    const DevTags& tg;
+    const uint8_t* buf;
+    int64_t total, ustart, n64;
+    unsigned long long* lastclose;  // per-warp shared array [kMaxCls]
+    int lane;
+    TokSrc ts;
+    bool overflow = false;
+    int64_t kept_len = 0;
+    uint8_t* dst = nullptr;
+    UnitDesc* desc = nullptr;  // count pass: where the trimmed runs go (copied later by the gather kernel)
+
+    __device__ StripRunWalker(const DevTags& tg_, const uint8_t* buf_, int64_t total_, int64_t ustart_, int64_t n_,
+                              unsigned long long* lc, int lane_, TokSrc ts_)
+        : tg(tg_), buf(buf_), total(total_), ustart(ustart_), n64(n_), lastclose(lc), lane(lane_), ts(ts_) {}
+
+    __device__ void run() {
+        if (n64 <= 0) return;
+        if (n64 >= (int64_t)1 << 31) {
+            overflow = true;
+            return;
+        }
+        const int n = (int)n64;
+        const PtrAcc T{buf + ustart};
+        const int64_t s_first = ustart >> 10, s_last = (ustart + n - 1) >> 10;
+        const bool one_group = s_last - s_first < 32;  // the usual case: all records stay in registers for both passes
+        for (int c = lane; c < tg.ncls; c += 32) lastclose[c] = 0;
+        __syncwarp();
+        int run_s = 0, run_e = 0, nruns = 0;  // lane i keeps run i
+        int state = -1, seg_start = 0;
+        int cnt = 0;
+        uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
+        for (int pass = 0; pass < 2; pass++) {
+            for (int64_t S0 = s_first; S0 <= s_last; S0 += 32) {
+                const int64_t sj = S0 + lane;
+                if (pass == 0 || !one_group) {
+                    cnt = 0;
+                    if (sj <= s_last) {
+                        cnt = ts.cnt[sj];
+                        if (cnt == kRecOverflow) cnt = -1;
+                        if (cnt > 0) {
+                            const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);
+                            ra = rp[0];
+                            if (cnt > 4) rb = rp[1];
+                        }
+                    }
+                    if (__any_sync(kFull, cnt < 0)) {
+                        overflow = true;
+                        return;
+                    }
+                }
+                const int sb0 = (int)((S0 << 10) - ustart);
+                if (pass == 0) {  // pass A: last closer per class, every lane over its own step
+                    for (int k = 0; k < cnt; k++) {
+                        const uint32_t r = rec_select(ra, rb, k);
+                        if (((r >> 17) & 3) != 1) continue;
+                        const int x = sb0 + lane * 1024 + (int)(r & 1023);
+                        const int tend = x + (int)((r >> 10) & 127);
+                        if (x >= 0 && tend <= n) atomicMax(&lastclose[(r >> 19) & 127], (unsigned long long)(x + 1));
+                    }
+                } else {  // pass B: tags in position order
+                    unsigned live = __ballot_sync(kFull, cnt > 0);
+                    while (live) {
+                        const int j = __ffs(live) - 1;
+                        live &= live - 1;
+                        const int c = __shfl_sync(kFull, cnt, j);
+#pragma unroll
+                        for (int k = 0; k < kRecPerStep; k++) {
+                            if (k >= c) break;
+                            const uint32_t r = __shfl_sync(kFull, rec_select(ra, rb, k), j);
+                            const int kind = (r >> 17) & 3;
+                            if (kind == 2) continue;
+                            const int x = sb0 + j * 1024 + (int)(r & 1023);
+                            const int tend = x + (int)((r >> 10) & 127);
+                            if (x < 0 || tend > n) continue;
+                            const int cls = (r >> 19) & 127;
+                            if (state < 0) {
+                                if (kind == 0 && lastclose[cls] > (unsigned long long)x) {  // live open tag
+                                    if (x > seg_start) {
+                                        if (lane == nruns) { run_s = seg_start; run_e = x; }
+                                        nruns++;
+                                    }
+                                    state = cls;
+                                }
+                            } else if (kind == 1 && cls == state) {
+                                seg_start = tend;
+                                state = -1;
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        if (n > seg_start) {
+            if (lane == nruns) { run_s = seg_start; run_e = n; }
+            nruns++;
+        }
+        if (nruns > (desc ? kDescRuns : 32)) {
+            overflow = true;
+            return;
+        }
+        // .strip(): drop white space from the front of the first runs and from the back of the last ones
+        int lead = nruns;  // first run that keeps anything
+        for (int i = 0; i < nruns; i++) {
+            const int rs = __shfl_sync(kFull, run_s, i), re = __shfl_sync(kFull, run_e, i);
+            int f = -1;
+            for (int base = rs; base < re; base += 32) {
+                const int x = base + lane;
+                const bool nw = x < re && !is_white_byte(T, x, n);
+                const unsigned b = __ballot_sync(kFull, nw);
+                if (b) { f = base + __ffs(b) - 1; break; }
+            }
+            if (f >= 0) {
+                if (lane == i) run_s = f;
+                lead = i;
+                break;
+            }
+            if (lane == i) run_e = run_s;  // all white
+        }
+        for (int i = nruns - 1; i >= lead; i--) {
+            const int rs = __shfl_sync(kFull, run_s, i), re = __shfl_sync(kFull, run_e, i);
+            int l = -1;
+            for (int top = re; top > rs; top -= 32) {
+                const int x = top - 32 + lane;
+                const bool nw = x >= rs && !is_white_byte(T, x, n);
+                const unsigned b = __ballot_sync(kFull, nw);
+                if (b) { l = top - 32 + (31 - __clz(b)); break; }
+            }
+            if (l >= 0) {
+                if (lane == i) run_e = l + 1;
+                break;
+            }
+            if (lane == i) run_e = run_s;
+        }
+        const int mylen = lane < nruns ? run_e - run_s : 0;
+        int incl = mylen;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int t = __shfl_up_sync(kFull, incl, d);
+            if (lane >= d) incl += t;
+        }
+        kept_len = __shfl_sync(kFull, incl, 31);
+        if (desc) {
+            UnitDesc& d = *desc;
+            if (lane == 0) {
+                d.nruns = nruns;
+                d.total = (int32_t)kept_len;
+                d.held_kept = 0;
+                d.depth = 0;
+                d.last_tok_end = -1;
+                d.rlast = n;
+                d.flags = 0;
+                d.pad = 0;
+            }
+            if (lane < kDescRuns) {
+                d.run_s[lane] = lane < nruns ? run_s : 0;
+                d.run_e[lane] = lane < nruns ? run_e : 0;
+            }
+        }
+        if (COPY) {
+            const int my_off = incl - mylen;
+            for (int i = 0; i < nruns; i++) {
+                const int rs = __shfl_sync(kFull, run_s, i), re = __shfl_sync(kFull, run_e, i), ro = __shfl_sync(kFull, my_off, i);
+                if (re > rs) warp_copy<true>(dst + ro, T.p + rs, re - rs, buf + total, lane);
+            }
+        }
     }
 };
 

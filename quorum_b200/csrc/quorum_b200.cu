@@ -48,13 +48,13 @@ static int fail(int code, const char* fmt, const char* a = "") {
 // ---------------------------------------------------------------------------------------------------------------
 __device__ __noinline__ StripResult strip_count_slow(const DevTags& tg, const uint8_t* in, int64_t total, int64_t a, int64_t n,
                                                      unsigned long long* lc, int lane) {
-    StripWalker<false, false> w(tg, in, total, a, n, lc, lane);
+    StripWalker<false> w(tg, in, total, a, n, lc, lane);
     w.run();
     return w.res;
 }
 __device__ __noinline__ void strip_copy_slow(const DevTags& tg, const uint8_t* in, int64_t total, int64_t a, int64_t n,
                                              unsigned long long* lc, int lane, int64_t first, int64_t kl, uint8_t* dst) {
-    StripWalker<true, false> w(tg, in, total, a, n, lc, lane);
+    StripWalker<true> w(tg, in, total, a, n, lc, lane);
     w.res.first_pos = first;
     w.res.kept_len = kl;
     w.dst = dst;
@@ -62,13 +62,13 @@ __device__ __noinline__ void strip_copy_slow(const DevTags& tg, const uint8_t* i
 }
 __device__ __noinline__ StreamResult stream_count_slow(const DevTags& tg, const uint8_t* bytes, int64_t total, const int64_t* co,
                                                        int64_t m, int lane, uint32_t flags, const StreamState* st_in) {
-    StreamWalker<false, false> w(tg, bytes, total, co, m, lane, flags);
+    StreamWalker<false> w(tg, bytes, total, co, m, lane, flags);
     return w.run(st_in, nullptr);
 }
 __device__ __noinline__ void stream_copy_slow(const DevTags& tg, const uint8_t* bytes, int64_t total, const int64_t* co, int64_t m,
                                               int lane, uint32_t flags, const StreamState* st_in, StreamState* st_out,
                                               int64_t base, uint8_t* out, int64_t* out_chunk_off, int64_t c0) {
-    StreamWalker<true, false> w(tg, bytes, total, co, m, lane, flags);
+    StreamWalker<true> w(tg, bytes, total, co, m, lane, flags);
     w.out_base = base;
     w.dst = out + base;
     w.out_chunk_off = out_chunk_off;
@@ -85,20 +85,27 @@ constexpr int kThreads = kWarpsPerBlock * 32;
 // scratch layout for strip_concat: int64 klen[n_resp] | int64 first[n_resp] | int64 dst[n_resp] | int64 reqlen[n_req+1]
 __global__ void __launch_bounds__(kThreads)
 strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
-                   int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first, TokSrc ts) {
+                   int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first, TokSrc ts,
+                   UnitDesc* __restrict__ desc) {
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
     for (int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib; r < n_resp; r += (int64_t)gridDim.x * kWarpsPerBlock) {
         const int64_t a = in_off[r], b = in_off[r + 1];
         StripResult res;
-        if (ts.cnt && !unit_has_overflow(ts, a, b - a, lane)) {
-            StripWalker<false, true> w(tg, in, total, a, b - a, lastclose[wib], lane);
-            w.ts = ts;
+        bool slow = ts.cnt == nullptr;
+        if (!slow) {
+            StripRunWalker<false> w(tg, in, total, a, b - a, lastclose[wib], lane, ts);
+            w.desc = desc + r;
+            if (b == a && lane == 0) desc[r].nruns = 0;  // empty response: nothing to walk, nothing to copy
             w.run();
-            res = w.res;
-        } else {
+            res.kept_len = w.kept_len;
+            res.first_pos = 0;
+            slow = w.overflow;
+        }
+        if (slow) {
             res = strip_count_slow(tg, in, total, a, b - a, lastclose[wib], lane);
+            if (desc && lane == 0) desc[r].nruns = -1;  // redone from the bytes by the copy kernel
         }
         if (lane == 0) {
             klen[r] = res.kept_len;
@@ -124,8 +131,8 @@ __global__ void request_layout_kernel(const int64_t* __restrict__ in_off, const 
             continue;
         }
         if (!first) o += sep_len;
+        dst[r] = (o << 1) | (first ? 0 : 1);  // bit 0: a separator sits right before this response's text
         first = false;
-        dst[r] = o;
         o += hide ? klen[r] : len;
     }
     reqlen[q] = o;
@@ -179,60 +186,65 @@ __global__ void request_finalize_kernel(const int64_t* __restrict__ req_off, int
     const int64_t r0 = req_off ? req_off[q] : q, r1 = req_off ? req_off[q + 1] : q + 1;
     const int64_t base = out_off[q];
     for (int64_t r = r0; r < r1; r++)
-        if (dst[r] >= 0) dst[r] += base;
+        if (dst[r] >= 0) dst[r] += base << 1;
 }
 
+// Warp-cooperative copy of a unit's kept runs (descriptor) to dst: run i goes to dst + held_kept + (lengths before it).
+__device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, const uint8_t* src, uint8_t* dst,
+                                            const uint8_t* src_hi, int lane) {
+    const int nruns = dp->nruns;
+    if (nruns <= 0) return;
+    int rs = 0, re = 0;
+    if (lane < kDescRuns && lane < nruns) {
+        rs = dp->run_s[lane];
+        re = dp->run_e[lane];
+        if ((dp->flags & 2) && lane == nruns - 1 && dp->rlast < re) re = dp->rlast > rs ? dp->rlast : rs;  // open-ended final run
+    }
+    const int len = re - rs;
+    int incl = len;
+#pragma unroll
+    for (int d = 1; d < kDescRuns; d <<= 1) {
+        int t = __shfl_up_sync(kFull, incl, d);
+        if (lane >= d) incl += t;
+    }
+    const int off = dp->held_kept + incl - len;
+    for (int i = 0; i < nruns; i++) {
+        const int s_i = __shfl_sync(kFull, rs, i), l_i = __shfl_sync(kFull, len, i), o_i = __shfl_sync(kFull, off, i);
+        if (l_i > 0) warp_copy<true>(dst + o_i, src + s_i, l_i, src_hi, lane);
+    }
+}
+
+// strip + concat, last kernel: every response's kept runs (and the separator in front of it) go to their final place.
 __global__ void __launch_bounds__(kThreads)
 strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
                   int64_t n_resp, const int64_t* __restrict__ klen, const int64_t* __restrict__ first,
                   const int64_t* __restrict__ dst, int hide, const uint8_t* __restrict__ sep, int32_t sep_len,
-                  uint8_t* __restrict__ out, int64_t* __restrict__ resp_out_len, TokSrc ts) {
+                  uint8_t* __restrict__ out, int64_t* __restrict__ resp_out_len, const UnitDesc* __restrict__ desc) {
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
     for (int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib; r < n_resp; r += (int64_t)gridDim.x * kWarpsPerBlock) {
         const int64_t a = in_off[r], b = in_off[r + 1];
-        const int64_t d = dst[r];
-        if (d < 0) {  // excluded from the join
+        const int64_t de = dst[r];
+        if (de < 0) {  // excluded from the join
             if (resp_out_len && lane == 0) resp_out_len[r] = 0;
             continue;
         }
-        // a separator precedes every included response that is not the first included one of its request:
-        // request_layout_kernel left room for it right before dst[r]
+        const int64_t d = de >> 1;
+        if (de & 1)  // the separator between this response and the previous included one of its request
+            for (int i = lane; i < sep_len; i += 32) out[d - sep_len + i] = sep[i];
         const int64_t kl = hide ? klen[r] : (b - a);
         if (resp_out_len && lane == 0) resp_out_len[r] = kl;
-        if (hide) {
-            if (kl > 0) {
-                if (ts.cnt && !unit_has_overflow(ts, a, b - a, lane)) {
-                    StripWalker<true, true> w(tg, in, total, a, b - a, lastclose[wib], lane);
-                    w.ts = ts;
-                    w.res.first_pos = first[r];
-                    w.res.kept_len = kl;
-                    w.dst = out + d;
-                    w.run();
-                } else {
-                    strip_copy_slow(tg, in, total, a, b - a, lastclose[wib], lane, first[r], kl, out + d);
-                }
+        if (!hide) {
+            warp_copy<true>(out + d, in + a, b - a, in + total, lane);
+        } else if (kl > 0) {
+            if (desc && desc[r].nruns >= 0) {
+                gather_unit(desc + r, in + a, out + d, in + total, lane);
+            } else {
+                strip_copy_slow(tg, in, total, a, b - a, lastclose[wib], lane, first[r], kl, out + d);
             }
-        } else {
-            warp_copy(out + d, in + a, b - a, in + total, lane);
         }
         __syncwarp();
-    }
-}
-
-// separators: thread per response; writes sep right before dst[r] when r is not the first included response of its request
-__global__ void separator_kernel(const int64_t* __restrict__ req_off, int64_t n_req, const int64_t* __restrict__ dst,
-                                 const uint8_t* __restrict__ sep, int32_t sep_len, uint8_t* __restrict__ out) {
-    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= n_req) return;
-    const int64_t r0 = req_off ? req_off[q] : q, r1 = req_off ? req_off[q + 1] : q + 1;
-    bool first = true;
-    for (int64_t r = r0; r < r1; r++) {
-        if (dst[r] < 0) continue;
-        if (!first)
-            for (int i = 0; i < sep_len; i++) out[dst[r] - sep_len + i] = sep[i];
-        first = false;
     }
 }
 
@@ -243,7 +255,7 @@ __global__ void __launch_bounds__(kThreads, 3)
 stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                     const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                     int64_t n_streams, const StreamState* __restrict__ st_in, uint32_t flags,
-                    int64_t* __restrict__ totals, TokSrc ts) {
+                    int64_t* __restrict__ totals, TokSrc ts, UnitDesc* __restrict__ desc) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
     for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
@@ -251,11 +263,16 @@ stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restric
         StreamResult r;
         bool slow = ts.cnt == nullptr;
         if (!slow) {
-            StreamRunWalker<false> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
+            StreamRunWalker<0> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
+            w.desc = desc + s;
+            if (c1 <= c0 && lane == 0) desc[s].nruns = 0;  // nothing fed: state passes through, nothing to copy
             r = w.run(st_in ? st_in + s : nullptr, nullptr);
-            slow = w.overflow;  // a step ran out of record slots: redo this unit from its bytes
+            slow = w.overflow;  // does not fit the descriptor: redo this unit from its bytes
         }
-        if (slow) r = stream_count_slow(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, st_in ? st_in + s : nullptr);
+        if (slow) {
+            r = stream_count_slow(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, st_in ? st_in + s : nullptr);
+            if (desc && lane == 0) desc[s].nruns = -1;
+        }
         if (lane == 0) totals[s] = r.total_out;
         __syncwarp();
     }
@@ -266,7 +283,7 @@ stream_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
                    const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                    int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
                    const int64_t* __restrict__ bases, uint8_t* __restrict__ out, int64_t* __restrict__ out_chunk_off,
-                   TokSrc ts) {
+                   TokSrc ts, UnitDesc* __restrict__ desc) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
     for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
@@ -274,15 +291,15 @@ stream_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
         // state_in may alias state_out: the walker reads its input state before writing the output state
         StreamState si;
         if (st_in) si = st_in[s];
-        bool slow = ts.cnt == nullptr;
-        if (!slow) {
-            StreamRunWalker<true> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
+        const bool slow = ts.cnt == nullptr || desc[s].nruns < 0;
+        if (!slow) {  // per-chunk offsets, carried literal bytes, carried state; the kept runs go through the gather kernel
+            StreamRunWalker<1> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
+            w.desc = desc + s;
             w.out_base = bases[s];
             w.dst = out + bases[s];
             w.out_chunk_off = out_chunk_off;
             w.chunk0 = c0;
             w.run(st_in ? &si : nullptr, st_out ? st_out + s : nullptr);
-            slow = w.overflow;  // rewritten below from the bytes: same base, same offsets
         }
         if (slow)
             stream_copy_slow(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, st_in ? &si : nullptr,
@@ -290,6 +307,20 @@ stream_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
         __syncwarp();
     }
     if (blockIdx.x == 0 && threadIdx.x == 0 && n_streams == 0) out_chunk_off[0] = 0;
+}
+
+// kept runs of every stream -> their final place (descriptor-driven; units redone by the slow walker are skipped)
+__global__ void __launch_bounds__(kThreads)
+stream_gather_kernel(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ chunk_off, int64_t n_chunks,
+                     const int64_t* __restrict__ stream_off, int64_t n_streams, const int64_t* __restrict__ bases,
+                     const UnitDesc* __restrict__ desc, uint8_t* __restrict__ out) {
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t total = chunk_off[n_chunks];
+    for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
+        if (desc[s].nruns <= 0) continue;
+        const int64_t a = chunk_off[stream_off[s]];
+        gather_unit(desc + s, bytes + a, out + bases[s], bytes + total, lane);
+    }
 }
 
 __global__ void stream_flush_kernel(StreamState* st, int64_t n) {
@@ -428,8 +459,10 @@ static size_t strip_general_scratch_bytes(int64_t n_resp, int64_t n_req) {
     return 3 * align256((size_t)(n_resp + 1) * 8) + align256((size_t)(n_req + 2) * 8) + 256;
 }
 
+static size_t desc_scratch_bytes(int64_t n_units) { return align256((size_t)(n_units < 0 ? 0 : n_units) * sizeof(UnitDesc) + 96); }
+
 size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req, int64_t out_capacity) {
-    return strip_general_scratch_bytes(n_resp, n_req) + tok_scratch_bytes(out_capacity) + 256;
+    return strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp) + tok_scratch_bytes(out_capacity) + 256;
 }
 
 static int grid_for(int64_t units) {
@@ -473,11 +506,13 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     const int sj = (flags & QB200_STREAM_JOIN) ? 1 : 0;
 
     TokSrc ts;
+    UnitDesc* desc = (UnitDesc*)((uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req));
     if (hide && n_resp > 0 && path_choice() != 0)
         ts = launch_tokenizer(tags->dev, in_bytes, in_off + n_resp, out_capacity,
-                              (uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req), stream);
+                              (uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp), stream);
     if (hide && n_resp > 0) {
-        strip_count_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts);
+        strip_count_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts,
+                                                                     ts.cnt ? desc : nullptr);
         LAUNCHED();
     }
     const int tb = 256;
@@ -490,11 +525,8 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     LAUNCHED();
     if (n_resp > 0) {
         strip_copy_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, dst,
-                                                                    hide, sep, sep_len, out_bytes, resp_out_len, ts);
-        LAUNCHED();
-    }
-    if (sep_len > 0 && req_off) {
-        separator_kernel<<<rg, tb, 0, stream>>>(req_off, n_req, dst, sep, sep_len, out_bytes);
+                                                                    hide, sep, sep_len, out_bytes, resp_out_len,
+                                                                    (hide && ts.cnt) ? desc : nullptr);
         LAUNCHED();
     }
     CUDA_TRY(cudaGetLastError());
@@ -514,7 +546,7 @@ static size_t tile_scratch_bytes(int64_t max_tiles) { return align256((size_t)(m
 size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity) {
     (void)n_chunks;
     return stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity)) +
-           tok_scratch_bytes(out_capacity) + 256;
+           desc_scratch_bytes(n_streams) + tok_scratch_bytes(out_capacity) + 256;
 }
 
 static int stream_feed_check(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
@@ -553,18 +585,26 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     const StreamState* si = reinterpret_cast<const StreamState*>(state_in);
     StreamState* so = reinterpret_cast<StreamState*>(state_out);
     TokSrc ts;
-    if (use_tokens) {  // records live behind the general + tile scratch regions (see qb200_stream_feed_scratch_bytes)
+    UnitDesc* desc = nullptr;
+    if (use_tokens) {  // descriptors + records live behind the general + tile scratch regions
         uint8_t* tsp = (uint8_t*)scratch + stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity));
-        ts = launch_tokenizer(tags->dev, chunk_bytes, chunk_off + n_chunks, out_capacity, tsp, stream);
+        desc = (UnitDesc*)tsp;
+        ts = launch_tokenizer(tags->dev, chunk_bytes, chunk_off + n_chunks, out_capacity, tsp + desc_scratch_bytes(n_streams),
+                              stream);
     }
     stream_count_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
-                                                                     n_streams, si, flags, totals, ts);
+                                                                     n_streams, si, flags, totals, ts, desc);
     LAUNCHED();
     scan_kernel<<<1, 1024, 0, stream>>>(totals, n_streams, bases);
     LAUNCHED();
     stream_copy_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
-                                                                    n_streams, si, so, flags, bases, out_bytes, out_chunk_off, ts);
+                                                                    n_streams, si, so, flags, bases, out_bytes, out_chunk_off, ts, desc);
     LAUNCHED();
+    if (use_tokens) {
+        stream_gather_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(chunk_bytes, chunk_off, n_chunks, stream_off, n_streams,
+                                                                          bases, desc, out_bytes);
+        LAUNCHED();
+    }
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
 }

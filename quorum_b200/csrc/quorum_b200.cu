@@ -138,9 +138,34 @@ __global__ void request_layout_kernel(const int64_t* __restrict__ in_off, const 
     reqlen[q] = o;
 }
 
-// single-block exclusive scan of v[0..n) into out[0..n], out[n] = total.  Warp w owns a contiguous slice and walks it
-// with coalesced 32-wide loads + a shuffle scan; the 32 slice sums are combined once in shared memory.
-__global__ void __launch_bounds__(1024) scan_kernel(const int64_t* __restrict__ v, int64_t n, int64_t* __restrict__ out) {
+// Exclusive scan of v[0..n) into out[0..n], out[n] = total, in three small launches:
+//   scan_partials_kernel   block b sums its slice of kScanSlice elements            -> partial[b]
+//   scan_kernel            one block scans the (few) partials in place               -> partial[b] = offset of slice b
+//   scan_apply_kernel      block b rescans its slice with that offset
+constexpr int kScanSlice = 8192;  // elements per block (256 threads x 32)
+
+__global__ void __launch_bounds__(256) scan_partials_kernel(const int64_t* __restrict__ v, int64_t n, int64_t* __restrict__ partial) {
+    __shared__ int64_t ws[8];
+    const int64_t a = (int64_t)blockIdx.x * kScanSlice;
+    int64_t sum = 0;
+#pragma unroll 4
+    for (int k = 0; k < kScanSlice / 256; k++) {
+        const int64_t i = a + k * 256 + threadIdx.x;
+        if (i < n) sum += v[i];
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(kFull, sum, d);
+    if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int64_t t = 0;
+        for (int w = 0; w < 8; w++) t += ws[w];
+        partial[blockIdx.x] = t;
+    }
+}
+
+// single-block exclusive scan (in place allowed: out may alias v); out[n] = total.  Warp w owns a contiguous slice.
+__global__ void __launch_bounds__(1024) scan_kernel(const int64_t* v, int64_t n, int64_t* out) {
     __shared__ int64_t warp_excl[32];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int64_t per = ((n + 31) / 32 + 31) / 32 * 32;  // slice length, a multiple of 32
@@ -151,6 +176,7 @@ __global__ void __launch_bounds__(1024) scan_kernel(const int64_t* __restrict__ 
     for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(kFull, sum, d);
     if (lane == 0) warp_excl[wid] = sum;
     __syncthreads();
+    int64_t total = 0;
     if (wid == 0) {
         const int64_t ws = warp_excl[lane];
         int64_t wi = ws;
@@ -160,7 +186,7 @@ __global__ void __launch_bounds__(1024) scan_kernel(const int64_t* __restrict__ 
             if (lane >= d) wi += t;
         }
         warp_excl[lane] = wi - ws;
-        if (lane == 31) out[n] = wi;
+        total = wi;
     }
     __syncthreads();
     int64_t run = warp_excl[wid];
@@ -176,6 +202,54 @@ __global__ void __launch_bounds__(1024) scan_kernel(const int64_t* __restrict__ 
         if (i < b) out[i] = run + incl - x;
         run += __shfl_sync(kFull, incl, 31);
     }
+    __syncthreads();
+    if (wid == 0 && lane == 31) out[n] = total;
+}
+
+__global__ void __launch_bounds__(256) scan_apply_kernel(const int64_t* __restrict__ v, int64_t n, const int64_t* __restrict__ partial,
+                                                         int64_t nblocks, int64_t* __restrict__ out) {
+    __shared__ int64_t ws[8];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int64_t a = (int64_t)blockIdx.x * kScanSlice;
+    int64_t run = partial[blockIdx.x];
+    for (int k = 0; k < kScanSlice / 256; k++) {
+        const int64_t i = a + k * 256 + threadIdx.x;
+        const int64_t x = i < n ? v[i] : 0;
+        int64_t incl = x;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int64_t t = __shfl_up_sync(kFull, incl, d);
+            if (lane >= d) incl += t;
+        }
+        if (lane == 31) ws[wid] = incl;
+        __syncthreads();
+        int64_t before = 0, all = 0;
+        for (int w = 0; w < 8; w++) {
+            const int64_t t = ws[w];
+            if (w < wid) before += t;
+            all += t;
+        }
+        if (i < n) out[i] = run + before + incl - x;
+        run += all;
+        __syncthreads();
+    }
+    if (blockIdx.x == nblocks - 1 && threadIdx.x == 0) out[n] = partial[nblocks];
+}
+
+// host helper: out[0..n] = exclusive scan of v[0..n); `partial` needs n / kScanSlice + 2 entries
+static void launch_scan(const int64_t* v, int64_t n, int64_t* out, int64_t* partial, cudaStream_t stream) {
+    if (n <= 4 * kScanSlice) {
+        scan_kernel<<<1, 1024, 0, stream>>>(v, n, out);
+        LAUNCHED();
+        return;
+    }
+    const int64_t nb = (n + kScanSlice - 1) / kScanSlice;
+    scan_partials_kernel<<<(unsigned)nb, 256, 0, stream>>>(v, n, partial);
+    LAUNCHED();
+    scan_kernel<<<1, 1024, 0, stream>>>(partial, nb, partial);
+    LAUNCHED();
+    scan_apply_kernel<<<(unsigned)nb, 256, 0, stream>>>(v, n, partial, nb, out);
+    LAUNCHED();
 }
 
 // dst[r] += out_off[request of r]   (thread per request)
@@ -456,7 +530,7 @@ static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const in
 static size_t strip_general_scratch_bytes(int64_t n_resp, int64_t n_req) {
     if (n_resp < 0) n_resp = 0;
     if (n_req < 0) n_req = 0;
-    return 3 * align256((size_t)(n_resp + 1) * 8) + align256((size_t)(n_req + 2) * 8) + 256;
+    return 3 * align256((size_t)(n_resp + 1) * 8) + align256((size_t)(n_req + 2) * 8) + align256((size_t)(n_req / kScanSlice + 4) * 8) + 256;
 }
 
 static size_t desc_scratch_bytes(int64_t n_units) { return align256((size_t)(n_units < 0 ? 0 : n_units) * sizeof(UnitDesc) + 96); }
@@ -519,8 +593,7 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     const unsigned rg = (unsigned)((n_req + tb - 1) / tb);
     request_layout_kernel<<<rg, tb, 0, stream>>>(in_off, req_off, n_req, klen, hide, sj, sep_len, dst, reqlen);
     LAUNCHED();
-    scan_kernel<<<1, 1024, 0, stream>>>(reqlen, n_req, out_off);
-    LAUNCHED();
+    launch_scan(reqlen, n_req, out_off, (int64_t*)((uint8_t*)reqlen + align256((size_t)(n_req + 2) * 8)), stream);
     request_finalize_kernel<<<rg, tb, 0, stream>>>(req_off, n_req, out_off, dst);
     LAUNCHED();
     if (n_resp > 0) {
@@ -535,7 +608,7 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
 
 static size_t stream_general_scratch_bytes(int64_t n_streams) {
     if (n_streams < 0) n_streams = 0;
-    return 2 * align256((size_t)(n_streams + 2) * 8) + 256;
+    return 2 * align256((size_t)(n_streams + 2) * 8) + align256((size_t)(n_streams / kScanSlice + 4) * 8) + 256;
 }
 
 static int64_t tiles_for(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte_bound) / kWindow + 2; }
@@ -595,8 +668,7 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     stream_count_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
                                                                      n_streams, si, flags, totals, ts, desc);
     LAUNCHED();
-    scan_kernel<<<1, 1024, 0, stream>>>(totals, n_streams, bases);
-    LAUNCHED();
+    launch_scan(totals, n_streams, bases, (int64_t*)((uint8_t*)bases + align256((size_t)(n_streams + 2) * 8)), stream);
     stream_copy_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
                                                                     n_streams, si, so, flags, bases, out_bytes, out_chunk_off, ts, desc);
     LAUNCHED();
@@ -697,7 +769,7 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
 //   * the first call on a device resolves the array's device address (set-up, once per device, with that device
 //     current).  Make that first call outside any stream capture.
 // ---------------------------------------------------------------------------------------------------------------
-#define QB200_NOALLOC_SCRATCH_BYTES_ (2 * (((QB200_NOALLOC_MAX_STREAMS + 2) * 8 + 255) / 256 * 256) + 256)
+#define QB200_NOALLOC_SCRATCH_BYTES_ (2 * (((QB200_NOALLOC_MAX_STREAMS + 2) * 8 + 255) / 256 * 256) + 1024)
 static __device__ __align__(256) unsigned char g_noalloc_scratch[QB200_NOALLOC_SCRATCH_BYTES_];
 
 static constexpr int kMaxDevices = 64;

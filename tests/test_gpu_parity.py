@@ -34,7 +34,7 @@ def dev():
 
 
 def _t(a, dev):
-    return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    return torch.from_numpy(np.array(a, copy=True)).to(dev)
 
 
 # ---------------------------------------------------------------------------------------------------------------

@@ -1,0 +1,172 @@
+"""The three implementations behind the C ABI must agree bit for bit: the record-driven pipeline (default), the fused
+single-pass tile kernel (QB200_PATH=tile, streams) and the byte-rescanning walkers (QB200_PATH=general, also what the
+other two fall back to for units that do not fit their tables).  Also: full BASELINE.json sizes with sampled oracle checks
+and size-independent properties."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def qb():
+    import quorum_b200
+    from quorum_b200 import _lib
+    _lib.lib()
+    return quorum_b200
+
+
+@pytest.fixture()
+def path_env():
+    old = os.environ.get("QB200_PATH")
+    yield
+    if old is None:
+        os.environ.pop("QB200_PATH", None)
+    else:
+        os.environ["QB200_PATH"] = old
+
+
+def _t(a, dev):
+    return torch.from_numpy(np.ascontiguousarray(a).copy()).to(dev)
+
+
+def _stream_all_paths(qb, tags, data, chunk_off, stream_off, flush):
+    dev = torch.device("cuda", 0)
+    table = qb.batch.tag_table(tags)
+    res = {}
+    for path in ("token", "tile", "general"):
+        os.environ["QB200_PATH"] = path
+        out, oco, st = qb.batch.stream_feed_batch(table, _t(data, dev), _t(chunk_off, dev), _t(stream_off, dev), None,
+                                                  flush=flush)
+        torch.cuda.synchronize()
+        n = int(oco[-1].item())
+        res[path] = (out[:n].cpu().numpy(), oco.cpu().numpy(), st.cpu().numpy())
+    for path in ("tile", "general"):
+        for a, b in zip(res["token"], res[path]):
+            assert np.array_equal(a, b), path
+    return res["token"]
+
+
+def test_stream_paths_agree_on_cfg2_and_ragged_shapes(qb, path_env):
+    from oracle import c_oracle
+    from quorum_b200 import synth
+    base = synth.cfg2_base(96)
+    idx = synth.gather_units(base, 700, seed=5)
+    data = np.ascontiguousarray(base[idx]).reshape(-1)
+    chunk_off = np.arange(0, data.size + 1, 64, dtype=np.int64)
+    stream_off = np.arange(0, 700 * 256 + 1, 256, dtype=np.int64)
+    out, oco, _ = _stream_all_paths(qb, synth.TAGS5, data, chunk_off, stream_off, True)
+    exp_out, exp_oco, _ = c_oracle.stream_feed_batch(c_oracle.Tags(synth.TAGS5), data, chunk_off, stream_off, None,
+                                                     c_oracle.FLAG_FLUSH)
+    assert np.array_equal(oco, exp_oco) and np.array_equal(out, exp_out)
+    # ragged: adversarial units of 64 B .. 64 KiB cut into uneven chunks (some empty), odd alignment everywhere
+    rng = np.random.default_rng(3)
+    units = synth.cfg5_units(6 << 20, seed=77)
+    chunks, soff = [], [0]
+    for u in units:
+        p = 0
+        while p < len(u):
+            q = min(len(u), p + int(rng.integers(0, 200)))
+            while q < len(u) and (u[q] & 0xC0) == 0x80:
+                q += 1
+            chunks.append(u[p:q])
+            p = q
+        soff.append(len(chunks))
+    cdata, coff = synth.pack(chunks)
+    out, oco, _ = _stream_all_paths(qb, synth.TAGS5, cdata, coff, np.asarray(soff, dtype=np.int64), False)
+    exp_out, exp_oco, _ = c_oracle.stream_feed_batch(c_oracle.Tags(synth.TAGS5), cdata, coff,
+                                                     np.asarray(soff, dtype=np.int64), None, 0)
+    assert np.array_equal(oco, exp_oco) and np.array_equal(out, exp_out)
+
+
+def test_strip_paths_agree(qb, path_env):
+    from quorum_b200 import synth
+    dev = torch.device("cuda", 0)
+    units = synth.cfg5_units(8 << 20, seed=91) + [synth.make_unit(np.random.default_rng(2), 300000, 9, 0.5)]
+    data, in_off = synth.pack(units)
+    req_off = np.unique(np.concatenate([[0, len(units)], np.random.default_rng(1).integers(0, len(units), 200)])).astype(np.int64)
+    table = qb.batch.tag_table(synth.TAGS5)
+    sep = _t(np.frombuffer(synth.SEP_MULTIBYTE.encode(), dtype=np.uint8), dev)
+    res = {}
+    for path in ("token", "general"):
+        os.environ["QB200_PATH"] = path
+        out, off, rl = qb.batch.strip_concat_batch(table, _t(data, dev), _t(in_off, dev), _t(req_off, dev), sep, hide=True,
+                                                   streaming=True, want_resp_len=True)
+        torch.cuda.synchronize()
+        n = int(off[-1].item())
+        res[path] = (out[:n].cpu().numpy(), off.cpu().numpy(), rl.cpu().numpy()[: len(units)])
+    for a, b in zip(res["token"], res["general"]):
+        assert np.array_equal(a, b)
+
+
+def test_record_slot_overflow_falls_back(qb):
+    """More '<' per KiB than the tokenizer has record slots for, and more kept runs than a descriptor holds."""
+    from oracle import c_oracle
+    from quorum_b200 import synth
+    dev = torch.device("cuda", 0)
+    tags = synth.TAGS5
+    dense = ("a<b <c> <<think>x</think>> </reason> <th " * 400).encode()            # '<' every few bytes
+    many_runs = ("keep <think>drop</think> " * 300).encode()                        # 300 kept runs in one unit
+    units = [dense, many_runs, b"plain text", dense[:1500], many_runs[:900]]
+    data, in_off = synth.pack(units)
+    exp = c_oracle.strip_concat_batch(c_oracle.Tags(tags), data, in_off, None, b"", c_oracle.FLAG_HIDE)
+    out, off, _ = qb.batch.strip_concat_batch(qb.batch.tag_table(tags), _t(data, dev), _t(in_off, dev), None, None, hide=True,
+                                              streaming=False)
+    torch.cuda.synchronize()
+    assert np.array_equal(off.cpu().numpy(), exp[1]) and np.array_equal(out[: int(exp[1][-1])].cpu().numpy(), exp[0])
+    chunk_off = np.unique(np.concatenate([in_off, np.arange(0, data.size, 97)])).astype(np.int64)
+    stream_off = np.searchsorted(chunk_off, in_off).astype(np.int64)
+    exp = c_oracle.stream_feed_batch(c_oracle.Tags(tags), data, chunk_off, stream_off, None, 0)
+    out, oco, st = qb.batch.stream_feed_batch(qb.batch.tag_table(tags), _t(data, dev), _t(chunk_off, dev), _t(stream_off, dev),
+                                              None, flush=False)
+    torch.cuda.synchronize()
+    assert np.array_equal(oco.cpu().numpy(), exp[1]) and np.array_equal(out[: int(exp[1][-1])].cpu().numpy(), exp[0])
+    assert np.array_equal(st.cpu().numpy().reshape(-1).view(c_oracle.STATE_DTYPE)["depth"], exp[2]["depth"])
+
+
+def test_cfg2_full_size_sampled_against_oracle(qb):
+    """BASELINE.json configs[1] at full size (65,536 streams x 256 chunks x 64 B = 1 GiB): every per-chunk offset is
+    checked through size-independent properties, 3,000 random streams byte for byte against the oracle."""
+    from oracle import c_oracle
+    from quorum_b200 import synth
+    dev = torch.device("cuda", 0)
+    n_streams, chunks, cb = 65536, 256, 64
+    base = synth.cfg2_base(256)
+    idx = synth.gather_units(base, n_streams, seed=1000)
+    data = torch.from_numpy(base).to(dev).index_select(0, torch.from_numpy(idx).to(dev)).reshape(-1).contiguous()
+    chunk_off = torch.arange(0, data.numel() + 1, cb, dtype=torch.int64, device=dev)
+    stream_off = torch.arange(0, n_streams * chunks + 1, chunks, dtype=torch.int64, device=dev)
+    out, oco, st = qb.batch.stream_feed_batch(qb.batch.tag_table(synth.TAGS5), data, chunk_off, stream_off, None, flush=True)
+    torch.cuda.synchronize()
+    lens = oco[1:] - oco[:-1]
+    assert int(oco[0]) == 0 and bool((lens >= 0).all())                       # offsets are a monotone prefix
+    assert bool((lens <= cb + 23).all())                                      # a feed returns at most its chunk + a held tail
+    per_stream = lens.reshape(n_streams, chunks).sum(1)
+    # identical streams (same base unit) must give identical results wherever they sit in the batch
+    idx_t = torch.from_numpy(idx).to(dev)
+    ref_len = torch.zeros(base.shape[0], dtype=torch.int64, device=dev).scatter_(0, idx_t, per_stream)
+    assert torch.equal(ref_len[idx_t], per_stream)
+    # oracle on the base pool gives every stream's expected output
+    flat = np.ascontiguousarray(base).reshape(-1)
+    co = np.arange(0, flat.size + 1, cb, dtype=np.int64)
+    so = np.arange(0, base.shape[0] * chunks + 1, chunks, dtype=np.int64)
+    e_out, e_oco, e_st = c_oracle.stream_feed_batch(c_oracle.Tags(synth.TAGS5), flat, co, so, None, c_oracle.FLAG_FLUSH)
+    e_len = (e_oco[1:] - e_oco[:-1]).reshape(base.shape[0], chunks)
+    assert np.array_equal(per_stream.cpu().numpy(), e_len.sum(1)[idx])
+    assert int(oco[-1]) == int(e_len.sum(1)[idx].sum())
+    got_lens = lens.reshape(n_streams, chunks)
+    rng = np.random.default_rng(11)
+    sample = rng.integers(0, n_streams, 3000)
+    sl = got_lens[torch.from_numpy(sample).to(dev)].cpu().numpy()
+    assert np.array_equal(sl, e_len[idx[sample]])
+    oco_h = oco.cpu().numpy()
+    for s in sample[:400]:
+        b = idx[s]
+        a0, a1 = oco_h[s * chunks], oco_h[(s + 1) * chunks]
+        assert bytes(out[a0:a1].cpu().numpy()) == bytes(e_out[e_oco[b * chunks]: e_oco[(b + 1) * chunks]])
+    depth = st.cpu().numpy().reshape(-1).view(c_oracle.STATE_DTYPE)["depth"]
+    assert np.array_equal(depth, e_st["depth"][idx])

@@ -39,6 +39,7 @@ extern "C" {
 #define QB200_HIDE 1u        /* strip_concat: apply the filter + .strip()  (hide_final_think, oai_proxy.py:134-139) */
 #define QB200_STREAM_JOIN 2u /* strip_concat: streaming-final join, drop inputs that are empty BEFORE the filter (oai_proxy.py:760-764) */
 #define QB200_FLUSH 4u       /* stream_feed: apply ThinkingTagFilter.flush() after the last chunk (oai_proxy.py:739, 352-371) */
+#define QB200_CHAIN 8u       /* stream_feed: this call is one slice of a larger batch, see qb200_stream_feed_batch */
 
 typedef struct qb200_tags qb200_tags; /* opaque, host-side */
 
@@ -93,7 +94,12 @@ int qb200_strip_concat_batch(const qb200_tags *tags, const uint8_t *in_bytes, co
  * fed in order (stream_off[0] = 0, stream_off[n_streams] = n_chunks; a stream's chunks are contiguous).
  * state_in == NULL starts every stream fresh (depth 0, nothing held); state_out may alias state_in or be NULL.
  * Outputs: the return value of the feed of chunk c is out_bytes[out_chunk_off[c] .. out_chunk_off[c+1])
- * (n_chunks+1 entries).  out_capacity must be >= chunk_off[n_chunks] + QB200_HELD_MAX * n_streams. */
+ * (n_chunks+1 entries).  out_capacity must be >= chunk_off[n_chunks] + QB200_HELD_MAX * n_streams.
+ * QB200_CHAIN lets a host feed one large batch slice by slice (e.g. to overlap host<->device copies with compute): all
+ * arrays stay those of the WHOLE batch, `stream_off` points at the slice's first stream (its entries are still absolute
+ * chunk indices), `n_streams` is the slice's stream count, state pointers point at the slice's first stream, and the
+ * slice's output starts at out_chunk_off[stream_off[0]], which the previous slice's call wrote (the first slice is called
+ * without the flag).  Slices must be issued in order on one stream; only the slice's bytes need to be resident. */
 size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity);
 int qb200_stream_feed_batch(const qb200_tags *tags, const uint8_t *chunk_bytes, const int64_t *chunk_off,
                             int64_t n_chunks, const int64_t *stream_off, int64_t n_streams,

@@ -8,7 +8,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libquorum_b200.so")
 
-QB200_HIDE, QB200_STREAM_JOIN, QB200_FLUSH = 1, 2, 4
+QB200_HIDE, QB200_STREAM_JOIN, QB200_FLUSH, QB200_CHAIN = 1, 2, 4, 8
 HELD_MAX = 23
 STATE_BYTES = 32
 

@@ -11,7 +11,7 @@ from typing import List, Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import QB200_FLUSH, QB200_HIDE, QB200_STREAM_JOIN, STATE_BYTES, check, lib
+from ._lib import QB200_CHAIN, QB200_FLUSH, QB200_HIDE, QB200_STREAM_JOIN, STATE_BYTES, check, lib
 
 
 class TagTable:
@@ -132,13 +132,17 @@ def new_stream_state(n_streams: int, device) -> torch.Tensor:
 def stream_feed_batch(tags: TagTable, chunk_bytes: torch.Tensor, chunk_off: torch.Tensor, stream_off: torch.Tensor,
                       state: Optional[torch.Tensor] = None, *, flush: bool = False,
                       state_out: Optional[torch.Tensor] = None, out_bytes: Optional[torch.Tensor] = None,
-                      out_chunk_off: Optional[torch.Tensor] = None, scratch: Optional[torch.Tensor] = None):
+                      out_chunk_off: Optional[torch.Tensor] = None, scratch: Optional[torch.Tensor] = None,
+                      chain: bool = False):
     """ThinkingTagFilter.feed for every chunk of every stream, in order, state carried (qb200_stream_feed_batch).
 
     chunk_bytes: uint8[total]; chunk_off: int64[n_chunks+1]; stream_off: int64[n_streams+1] (chunk indices).
     state: uint8[n_streams, 32] from a previous call / new_stream_state, or None for fresh streams.
     Returns (out_bytes, out_chunk_off, state_out): the feed of chunk c returned
     out_bytes[out_chunk_off[c]:out_chunk_off[c+1]].
+    chain=True (QB200_CHAIN): this call is one slice of a larger batch — chunk_bytes / chunk_off / out_bytes /
+    out_chunk_off are the whole batch's tensors, stream_off (and the state tensors) are views of the slice's streams, and
+    the slice's output continues where the previous slice's call left out_chunk_off.
     """
     dev = chunk_off.device
     _require_cuda(chunk_off, torch.int64, "chunk_off")
@@ -162,8 +166,8 @@ def stream_feed_batch(tags: TagTable, chunk_bytes: torch.Tensor, chunk_off: torc
             scratch = torch.empty(need, dtype=torch.uint8, device=dev)
         check(lib().qb200_stream_feed_batch(
             tags.handle, _ptr(chunk_bytes), _ptr(chunk_off), n_chunks, _ptr(stream_off), n_streams, _ptr(state),
-            _ptr(state_out), QB200_FLUSH if flush else 0, _ptr(out_bytes), out_bytes.numel(), _ptr(out_chunk_off),
-            _ptr(scratch), scratch.numel(), _stream_ptr(dev)))
+            _ptr(state_out), (QB200_FLUSH if flush else 0) | (QB200_CHAIN if chain else 0), _ptr(out_bytes),
+            out_bytes.numel(), _ptr(out_chunk_off), _ptr(scratch), scratch.numel(), _stream_ptr(dev)))
     return out_bytes, out_chunk_off, state_out
 
 
@@ -242,21 +246,63 @@ class HostStreamFeeder:
         self.h_oco = torch.empty(max_chunks + 1, dtype=torch.int64).pin_memory()
 
     def run(self, h_data: torch.Tensor, h_chunk_off: torch.Tensor, h_stream_off: torch.Tensor, *, flush: bool,
-            carry_state: bool = False):
-        """Returns (h2d_bytes, d2h_bytes); results are in self.h_out[: self.h_oco[n_chunks]] and self.h_oco."""
+            carry_state: bool = False, slices: int = 8):
+        """Returns (h2d_bytes, d2h_bytes); results are in self.h_out[: self.h_oco[n_chunks]] and self.h_oco.
+
+        The batch is fed in `slices` slices of streams (QB200_CHAIN): while slice k is being filtered, slice k+1 is on
+        its way up and slice k-1's output on its way down (PCIe is full duplex), so the call costs about
+        max(upload, download) instead of their sum."""
         nb, nc, ns = h_data.numel(), h_chunk_off.numel() - 1, h_stream_off.numel() - 1
-        data, co, so = self.d_data[:nb], self.d_co[:nc + 1], self.d_so[:ns + 1]
-        data.copy_(h_data, non_blocking=True)
-        co.copy_(h_chunk_off, non_blocking=True)
-        so.copy_(h_stream_off, non_blocking=True)
-        state = self.d_state[:ns]
-        stream_feed_batch(self.tags, data, co, so, state if carry_state else None, flush=flush, state_out=state,
-                          out_bytes=self.d_out, out_chunk_off=self.d_oco[:nc + 1], scratch=self.d_scratch)
-        self.h_oco[:nc + 1].copy_(self.d_oco[:nc + 1], non_blocking=True)
-        torch.cuda.current_stream(self.dev).synchronize()
+        if ns < 4 * slices or nb < (1 << 22):
+            slices = 1
+        dev = self.dev
+        cur = torch.cuda.current_stream(dev)
+        if not hasattr(self, "_s_in"):
+            self._s_in, self._s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        s_in, s_out = self._s_in, self._s_out
+        s_in.wait_stream(cur)
+        s_out.wait_stream(cur)
+        d_data, d_co, d_so, d_oco = self.d_data[:nb], self.d_co[:nc + 1], self.d_so[:ns + 1], self.d_oco[:nc + 1]
+        with torch.cuda.stream(s_in):
+            d_so.copy_(h_stream_off, non_blocking=True)
+        sb = [ns * k // slices for k in range(slices + 1)]                      # stream bounds
+        cb = [int(h_stream_off[i]) for i in sb]                                # chunk bounds (host reads, pinned)
+        bb = [int(h_chunk_off[c]) for c in cb]                                 # byte bounds
+        ev_o, pending = [], None
+
+        def drain(k):                                                          # slice k's bytes -> host, once its end is known
+            ev_o[k].synchronize()
+            o0 = 0 if k == 0 else int(self.h_oco[cb[k]])
+            o1 = int(self.h_oco[cb[k + 1]])
+            with torch.cuda.stream(s_out):
+                self.h_out[o0:o1].copy_(self.d_out[o0:o1], non_blocking=True)
+
+        for k in range(slices):
+            with torch.cuda.stream(s_in):
+                d_data[bb[k]:bb[k + 1]].copy_(h_data[bb[k]:bb[k + 1]], non_blocking=True)
+                d_co[cb[k]:cb[k + 1] + 1].copy_(h_chunk_off[cb[k]:cb[k + 1] + 1], non_blocking=True)
+                ev_in = torch.cuda.Event()
+                ev_in.record(s_in)
+            cur.wait_event(ev_in)
+            st = self.d_state[sb[k]:sb[k + 1]]
+            stream_feed_batch(self.tags, d_data, d_co, d_so[sb[k]:sb[k + 1] + 1], st if carry_state else None, flush=flush,
+                              state_out=st, out_bytes=self.d_out, out_chunk_off=d_oco, scratch=self.d_scratch, chain=k > 0)
+            ev_c = torch.cuda.Event()
+            ev_c.record(cur)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_c)
+                lo = cb[k] + (1 if k else 0)
+                self.h_oco[lo:cb[k + 1] + 1].copy_(d_oco[lo:cb[k + 1] + 1], non_blocking=True)
+                e = torch.cuda.Event()
+                e.record(s_out)
+                ev_o.append(e)
+            if pending is not None:
+                drain(pending)
+            pending = k
+        drain(pending)
+        s_out.synchronize()
+        cur.wait_stream(s_out)
         total = int(self.h_oco[nc])
-        self.h_out[:total].copy_(self.d_out[:total], non_blocking=True)
-        torch.cuda.current_stream(self.dev).synchronize()
         return nb + 8 * (nc + 1) + 8 * (ns + 1), total + 8 * (nc + 1)
 
 

@@ -33,15 +33,18 @@ __device__ __forceinline__ int tag_at(const DevTags& tg, const uint8_t* buf, int
     return (int)(tend - x);
 }
 
+// The byte range to tokenize is [off[idx ? idx[0] : 0], off[idx ? idx[n] : n)): the units of this call (a chained call
+// covers a slice of the flat buffer, see QB200_CHAIN).  Bytes at and beyond the end are never read.
 __global__ void __launch_bounds__(256) tokenize_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
-                                                       const int64_t* __restrict__ total_ptr, uint8_t* __restrict__ cnt,
-                                                       uint32_t* __restrict__ rec, int64_t max_steps) {
+                                                       const int64_t* __restrict__ off, const int64_t* __restrict__ idx, int64_t n,
+                                                       uint8_t* __restrict__ cnt, uint32_t* __restrict__ rec, int64_t max_steps) {
     const int lane = threadIdx.x & 31;
-    const int64_t total = *total_ptr;
+    const int64_t begin = idx ? off[idx[0]] : off[0];
+    const int64_t total = idx ? off[idx[n]] : off[n];
     int64_t nsteps = (total + 1023) >> 10;
     if (nsteps > max_steps) nsteps = max_steps;
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
-    for (int64_t step = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); step < nsteps; step += nwarps) {
+    for (int64_t step = (begin >> 10) + (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); step < nsteps; step += nwarps) {
         const int64_t a = (step << 10) + lane * 32;
         uint32_t lt = 0;
         if (a + 32 <= total) {

@@ -165,8 +165,10 @@ __global__ void __launch_bounds__(256) scan_partials_kernel(const int64_t* __res
 }
 
 // single-block exclusive scan (in place allowed: out may alias v); out[n] = total.  Warp w owns a contiguous slice.
-__global__ void __launch_bounds__(1024) scan_kernel(const int64_t* v, int64_t n, int64_t* out) {
+__global__ void __launch_bounds__(1024) scan_kernel(const int64_t* v, int64_t n, int64_t* out, const int64_t* init_arr,
+                                                    const int64_t* init_idx) {
     __shared__ int64_t warp_excl[32];
+    const int64_t init = init_arr ? init_arr[init_idx ? *init_idx : 0] : 0;  // chained calls start at a given offset
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int64_t per = ((n + 31) / 32 + 31) / 32 * 32;  // slice length, a multiple of 32
     const int64_t a = (int64_t)wid * per, b = a + per < n ? a + per : n;
@@ -189,7 +191,7 @@ __global__ void __launch_bounds__(1024) scan_kernel(const int64_t* v, int64_t n,
         total = wi;
     }
     __syncthreads();
-    int64_t run = warp_excl[wid];
+    int64_t run = warp_excl[wid] + init;
     for (int64_t i0 = a; i0 < b; i0 += 32) {
         const int64_t i = i0 + lane;
         const int64_t x = i < b ? v[i] : 0;
@@ -203,15 +205,17 @@ __global__ void __launch_bounds__(1024) scan_kernel(const int64_t* v, int64_t n,
         run += __shfl_sync(kFull, incl, 31);
     }
     __syncthreads();
-    if (wid == 0 && lane == 31) out[n] = total;
+    if (wid == 0 && lane == 31) out[n] = total + init;
 }
 
 __global__ void __launch_bounds__(256) scan_apply_kernel(const int64_t* __restrict__ v, int64_t n, const int64_t* __restrict__ partial,
-                                                         int64_t nblocks, int64_t* __restrict__ out) {
+                                                         int64_t nblocks, int64_t* __restrict__ out, const int64_t* init_arr,
+                                                         const int64_t* init_idx) {
     __shared__ int64_t ws[8];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int64_t a = (int64_t)blockIdx.x * kScanSlice;
-    int64_t run = partial[blockIdx.x];
+    const int64_t init = init_arr ? init_arr[init_idx ? *init_idx : 0] : 0;
+    int64_t run = partial[blockIdx.x] + init;
     for (int k = 0; k < kScanSlice / 256; k++) {
         const int64_t i = a + k * 256 + threadIdx.x;
         const int64_t x = i < n ? v[i] : 0;
@@ -233,22 +237,23 @@ __global__ void __launch_bounds__(256) scan_apply_kernel(const int64_t* __restri
         run += all;
         __syncthreads();
     }
-    if (blockIdx.x == nblocks - 1 && threadIdx.x == 0) out[n] = partial[nblocks];
+    if (blockIdx.x == nblocks - 1 && threadIdx.x == 0) out[n] = partial[nblocks] + init;
 }
 
 // host helper: out[0..n] = exclusive scan of v[0..n); `partial` needs n / kScanSlice + 2 entries
-static void launch_scan(const int64_t* v, int64_t n, int64_t* out, int64_t* partial, cudaStream_t stream) {
+static void launch_scan(const int64_t* v, int64_t n, int64_t* out, int64_t* partial, cudaStream_t stream,
+                        const int64_t* init_arr = nullptr, const int64_t* init_idx = nullptr) {
     if (n <= 4 * kScanSlice) {
-        scan_kernel<<<1, 1024, 0, stream>>>(v, n, out);
+        scan_kernel<<<1, 1024, 0, stream>>>(v, n, out, init_arr, init_idx);
         LAUNCHED();
         return;
     }
     const int64_t nb = (n + kScanSlice - 1) / kScanSlice;
     scan_partials_kernel<<<(unsigned)nb, 256, 0, stream>>>(v, n, partial);
     LAUNCHED();
-    scan_kernel<<<1, 1024, 0, stream>>>(partial, nb, partial);
+    scan_kernel<<<1, 1024, 0, stream>>>(partial, nb, partial, nullptr, nullptr);
     LAUNCHED();
-    scan_apply_kernel<<<(unsigned)nb, 256, 0, stream>>>(v, n, partial, nb, out);
+    scan_apply_kernel<<<(unsigned)nb, 256, 0, stream>>>(v, n, partial, nb, out, init_arr, init_idx);
     LAUNCHED();
 }
 
@@ -510,8 +515,8 @@ static size_t tok_scratch_bytes(int64_t byte_bound) {
 }
 
 // tokenizer pass over the flat buffer; returns where the records are
-static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const int64_t* total_ptr, int64_t byte_bound,
-                               uint8_t* scratch, cudaStream_t stream) {
+static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const int64_t* off, const int64_t* idx, int64_t n,
+                               int64_t byte_bound, uint8_t* scratch, cudaStream_t stream) {
     const int64_t st = steps_for(byte_bound);
     TokSrc ts;
     uint8_t* cnt = scratch;
@@ -520,7 +525,7 @@ static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const in
     const int64_t cap = 148 * 8 * 4;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    tokenize_kernel<<<(unsigned)blocks, 256, 0, stream>>>(tg, bytes, total_ptr, cnt, rec, st);
+    tokenize_kernel<<<(unsigned)blocks, 256, 0, stream>>>(tg, bytes, off, idx, n, cnt, rec, st);
     LAUNCHED();
     ts.cnt = cnt;
     ts.rec = rec;
@@ -582,7 +587,7 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     TokSrc ts;
     UnitDesc* desc = (UnitDesc*)((uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req));
     if (hide && n_resp > 0 && path_choice() != 0)
-        ts = launch_tokenizer(tags->dev, in_bytes, in_off + n_resp, out_capacity,
+        ts = launch_tokenizer(tags->dev, in_bytes, in_off, nullptr, n_resp, out_capacity,
                               (uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp), stream);
     if (hide && n_resp > 0) {
         strip_count_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts,
@@ -645,9 +650,12 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     if (rc != QB200_OK) return rc;
     if (scratch_bytes < stream_general_scratch_bytes(n_streams) || !scratch)
         return fail(QB200_ESCRATCH, "stream_feed_batch: scratch too small");
+    const bool chain = (flags & QB200_CHAIN) != 0;
     if (n_streams == 0) {
-        set_i64_kernel<<<1, 1, 0, stream>>>(out_chunk_off, 0);
-        LAUNCHED();
+        if (!chain) {
+            set_i64_kernel<<<1, 1, 0, stream>>>(out_chunk_off, 0);
+            LAUNCHED();
+        }
         CUDA_TRY(cudaGetLastError());
         return QB200_OK;
     }
@@ -662,13 +670,15 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     if (use_tokens) {  // descriptors + records live behind the general + tile scratch regions
         uint8_t* tsp = (uint8_t*)scratch + stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity));
         desc = (UnitDesc*)tsp;
-        ts = launch_tokenizer(tags->dev, chunk_bytes, chunk_off + n_chunks, out_capacity, tsp + desc_scratch_bytes(n_streams),
-                              stream);
+        ts = launch_tokenizer(tags->dev, chunk_bytes, chunk_off, stream_off, n_streams, out_capacity,
+                              tsp + desc_scratch_bytes(n_streams), stream);
     }
     stream_count_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
                                                                      n_streams, si, flags, totals, ts, desc);
     LAUNCHED();
-    launch_scan(totals, n_streams, bases, (int64_t*)((uint8_t*)bases + align256((size_t)(n_streams + 2) * 8)), stream);
+    // chained call: this call's output starts where out_chunk_off[first chunk of the call] says (written by the call before)
+    launch_scan(totals, n_streams, bases, (int64_t*)((uint8_t*)bases + align256((size_t)(n_streams + 2) * 8)), stream,
+                chain ? out_chunk_off : nullptr, chain ? stream_off : nullptr);
     stream_copy_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
                                                                     n_streams, si, so, flags, bases, out_bytes, out_chunk_off, ts, desc);
     LAUNCHED();
@@ -697,7 +707,7 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
                             int64_t* out_chunk_off, void* scratch, size_t scratch_bytes, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     const int path = path_choice();
-    if (path != 1 || n_streams == 0) {
+    if (path != 1 || n_streams == 0 || (flags & QB200_CHAIN)) {
         const bool tok = path == 2 && n_streams > 0;
         if (tok && (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams, out_capacity) || !scratch))
             return fail(QB200_ESCRATCH, "stream_feed_batch: scratch too small (see qb200_stream_feed_scratch_bytes)");

@@ -170,3 +170,28 @@ def test_cfg2_full_size_sampled_against_oracle(qb):
         assert bytes(out[a0:a1].cpu().numpy()) == bytes(e_out[e_oco[b * chunks]: e_oco[(b + 1) * chunks]])
     depth = st.cpu().numpy().reshape(-1).view(c_oracle.STATE_DTYPE)["depth"]
     assert np.array_equal(depth, e_st["depth"][idx])
+
+
+def test_chained_slices_and_pipelined_host_feeder(qb):
+    """QB200_CHAIN: a batch fed slice by slice (what the host-buffer session does to overlap PCIe copies with compute)
+    gives the same bytes and the same per-chunk offsets as one call."""
+    from oracle import c_oracle
+    from quorum_b200 import synth
+    dev = torch.device("cuda", 0)
+    base = synth.cfg2_base(64)
+    idx = synth.gather_units(base, 640, seed=8)
+    data = np.ascontiguousarray(base[idx]).reshape(-1)
+    chunk_off = np.arange(0, data.size + 1, 64, dtype=np.int64)
+    stream_off = np.arange(0, 640 * 256 + 1, 256, dtype=np.int64)
+    exp_out, exp_oco, exp_st = c_oracle.stream_feed_batch(c_oracle.Tags(synth.TAGS5), data, chunk_off, stream_off, None, 0)
+    feeder = qb.batch.HostStreamFeeder(qb.batch.tag_table(synth.TAGS5), dev, data.size, len(chunk_off) - 1, 640)
+    pin = lambda a: torch.from_numpy(np.array(a, copy=True)).pin_memory()  # noqa: E731
+    for slices in (1, 5, 8):
+        feeder.h_out.zero_()
+        feeder.h_oco.zero_()
+        feeder.run(pin(data), pin(chunk_off), pin(stream_off), flush=False, slices=slices)
+        torch.cuda.synchronize()
+        assert np.array_equal(feeder.h_oco[: len(exp_oco)].numpy(), exp_oco), slices
+        assert np.array_equal(feeder.h_out[: int(exp_oco[-1])].numpy(), exp_out), slices
+        st = feeder.d_state[:640].cpu().numpy().reshape(-1).view(c_oracle.STATE_DTYPE)
+        assert np.array_equal(st["depth"], exp_st["depth"]) and np.array_equal(st["held_len"], exp_st["held_len"])

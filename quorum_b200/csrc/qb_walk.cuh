@@ -751,6 +751,14 @@ struct StreamRunWalker {
         int R_last = 0, P_last = 0;
         bool have_last = false;
         if (COPY && lane == 0) out_chunk_off[chunk0] = out_base;
+        // every lane gets its own copy of the (at most kDescRuns) runs: the boundary loop then needs no shuffles
+        int rsv[kDescRuns], rev[kDescRuns];
+#pragma unroll
+        for (int i = 0; i < kDescRuns; i++) {
+            rsv[i] = __shfl_sync(kFull, run_s, i);
+            rev[i] = __shfl_sync(kFull, run_e, i);
+            if (i >= nruns) rsv[i] = rev[i] = 0;
+        }
         const int64_t kb0 = COPY ? 1 : m;
         int64_t cnext = kb0 + lane <= m ? co[kb0 + lane] : 0;  // boundaries are fetched one batch ahead
         for (int64_t kb = kb0; kb <= m; kb += 32) {
@@ -784,11 +792,11 @@ struct StreamRunWalker {
             // '<' at p kept text (inside a run)?  One uniform loop over the runs for both.
             int P = held_kept;
             bool p_kept = false;
-            for (int i = 0; i < nruns; i++) {
-                const int rs = __shfl_sync(kFull, run_s, i), re = __shfl_sync(kFull, run_e, i);
-                const int hi = c < re ? c : re;
-                if (hi > rs) P += hi - rs;
-                p_kept |= (p >= rs && p < re);
+#pragma unroll
+            for (int i = 0; i < kDescRuns; i++) {
+                const int hi = min(c, rev[i]);
+                P += max(hi - rsv[i], 0);
+                p_kept |= (p >= rsv[i] && p < rev[i]);
             }
             int R = c;
             const bool found_lt = p >= 0;

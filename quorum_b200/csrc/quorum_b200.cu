@@ -142,7 +142,7 @@ __global__ void request_layout_kernel(const int64_t* __restrict__ in_off, const 
 //   scan_partials_kernel   block b sums its slice of kScanSlice elements            -> partial[b]
 //   scan_kernel            one block scans the (few) partials in place               -> partial[b] = offset of slice b
 //   scan_apply_kernel      block b rescans its slice with that offset
-constexpr int kScanSlice = 8192;  // elements per block (256 threads x 32)
+constexpr int kScanSlice = 2048;  // elements per block (256 threads x 8)
 
 __global__ void __launch_bounds__(256) scan_partials_kernel(const int64_t* __restrict__ v, int64_t n, int64_t* __restrict__ partial) {
     __shared__ int64_t ws[8];

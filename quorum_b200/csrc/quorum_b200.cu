@@ -83,7 +83,7 @@ constexpr int kWarpsPerBlock = 8;
 constexpr int kThreads = kWarpsPerBlock * 32;
 
 // scratch layout for strip_concat: int64 klen[n_resp] | int64 first[n_resp] | int64 dst[n_resp] | int64 reqlen[n_req+1]
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 5)
 strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
                    int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first, TokSrc ts,
                    UnitDesc* __restrict__ desc) {
@@ -287,6 +287,13 @@ __device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, con
         if (lane >= d) incl += t;
     }
     const int off = dp->held_kept + incl - len;
+    for (int i = 0; i < nruns; i++) {  // get every source line of every run moving before the first copy waits on one
+        const int s_i = __shfl_sync(kFull, rs, i), l_i = __shfl_sync(kFull, len, i);
+        const uint8_t* a = src + s_i;
+        const uint8_t* base = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(a) & ~(uintptr_t)127);
+        const int64_t bytes = (a - base) + l_i;
+        for (int64_t o = (int64_t)lane * 128; o < bytes; o += 32 * 128) asm volatile("prefetch.L2 [%0];" ::"l"(base + o));
+    }
     for (int i = 0; i < nruns; i++) {
         const int s_i = __shfl_sync(kFull, rs, i), l_i = __shfl_sync(kFull, len, i), o_i = __shfl_sync(kFull, off, i);
         if (l_i > 0) warp_copy<true>(dst + o_i, src + s_i, l_i, src_hi, lane);
@@ -294,7 +301,7 @@ __device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, con
 }
 
 // strip + concat, last kernel: every response's kept runs (and the separator in front of it) go to their final place.
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 5)
 strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
                   int64_t n_resp, const int64_t* __restrict__ klen, const int64_t* __restrict__ first,
                   const int64_t* __restrict__ dst, int hide, const uint8_t* __restrict__ sep, int32_t sep_len,
@@ -330,7 +337,7 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
 // ---------------------------------------------------------------------------------------------------------------
 // kernels: stream feed
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 3)
+__global__ void __launch_bounds__(kThreads, 4)
 stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                     const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                     int64_t n_streams, const StreamState* __restrict__ st_in, uint32_t flags,
@@ -357,7 +364,7 @@ stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restric
     }
 }
 
-__global__ void __launch_bounds__(kThreads, 3)
+__global__ void __launch_bounds__(kThreads, 4)
 stream_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                    const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                    int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
@@ -389,7 +396,7 @@ stream_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
 }
 
 // kept runs of every stream -> their final place (descriptor-driven; units redone by the slow walker are skipped)
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 5)
 stream_gather_kernel(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ chunk_off, int64_t n_chunks,
                      const int64_t* __restrict__ stream_off, int64_t n_streams, const int64_t* __restrict__ bases,
                      const UnitDesc* __restrict__ desc, uint8_t* __restrict__ out) {

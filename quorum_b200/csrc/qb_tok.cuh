@@ -46,6 +46,10 @@ __global__ void __launch_bounds__(256) tokenize_kernel(const __grid_constant__ D
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
     for (int64_t step = (begin >> 10) + (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); step < nsteps; step += nwarps) {
         const int64_t a = (step << 10) + lane * 32;
+        {   // this warp's next step: get its eight lines into L2 now, one iteration of work ahead of their use
+            const int64_t an = ((step + nwarps) << 10) + lane * 128;
+            if (lane < 8 && an + 128 <= total) asm volatile("prefetch.global.L2 [%0];" ::"l"(bytes + an));
+        }
         uint32_t lt = 0;
         if (a + 32 <= total) {
             const uint4* p = reinterpret_cast<const uint4*>(bytes + a);

@@ -82,6 +82,20 @@ __device__ __noinline__ void stream_copy_slow(const DevTags& tg, const uint8_t* 
 constexpr int kWarpsPerBlock = 8;
 constexpr int kThreads = kWarpsPerBlock * 32;
 
+// Software pipelining of the warp-per-unit loops: while unit r is being walked, the lines the NEXT unit of this warp will
+// touch first (its record counts, its records, the first and last bytes of its text) are already on their way.
+__device__ __forceinline__ void prefetch_unit_meta(const TokSrc& ts, const uint8_t* bytes, int64_t a, int64_t b, int lane) {
+    if (!ts.cnt || b <= a) return;
+    const int64_t s0 = a >> 10, s1 = (b - 1) >> 10;
+    const void* p = nullptr;
+    if (lane == 0) p = ts.cnt + s0;
+    else if (lane == 1) p = ts.cnt + s1;
+    else if (lane == 2) p = bytes + a;
+    else if (lane == 3) p = bytes + b - 1;
+    else if (s0 + (lane - 4) * 4 <= s1) p = ts.rec + (s0 + (lane - 4) * 4) * kRecPerStep;  // 4 steps of records per 128-byte line
+    if (p) asm volatile("prefetch.L1 [%0];" ::"l"(p));
+}
+
 // scratch layout for strip_concat: int64 klen[n_resp] | int64 first[n_resp] | int64 dst[n_resp] | int64 reqlen[n_req+1]
 __global__ void __launch_bounds__(kThreads, 5)
 strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
@@ -90,8 +104,16 @@ strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
-    for (int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib; r < n_resp; r += (int64_t)gridDim.x * kWarpsPerBlock) {
-        const int64_t a = in_off[r], b = in_off[r + 1];
+    const int64_t stride = (int64_t)gridDim.x * kWarpsPerBlock;
+    int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib;
+    int64_t a = 0, b = 0, an = 0, bn = 0;
+    if (r < n_resp) { a = in_off[r]; b = in_off[r + 1]; }
+    if (r + stride < n_resp) { an = in_off[r + stride]; bn = in_off[r + stride + 1]; }
+    for (; r < n_resp; r += stride) {
+        // offsets two units ahead (in flight while this unit is walked), record/text lines one unit ahead
+        int64_t ann = 0, bnn = 0;
+        if (r + 2 * stride < n_resp) { ann = in_off[r + 2 * stride]; bnn = in_off[r + 2 * stride + 1]; }
+        if (r + stride < n_resp) prefetch_unit_meta(ts, in, an, bn, lane);
         StripResult res;
         bool slow = ts.cnt == nullptr;
         if (!slow) {
@@ -112,6 +134,7 @@ strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
             first[r] = res.first_pos;
         }
         __syncwarp();
+        a = an; b = bn; an = ann; bn = bnn;
     }
 }
 

@@ -37,6 +37,9 @@ WORKLOADS = {
                  name="cfg3: 1M responses x 4 KB, 5 thinking_tags, 4 per request, multi-byte separator"),
     "cfg4": dict(kind="resp", units=131072, unit_bytes=32768, per_request=8, n_base=256,
                  name="cfg4: 8 backends x 32 KB reasoning-heavy (70% inside <think>), hide_final_think, 16384 requests"),
+    "cfg5": dict(kind="ragged", total_bytes=1250000000, pool_bytes=24 << 20, per_request=4,
+                 name="cfg5: adversarial mix (nested/unclosed/stray/crossed tags, fold characters, multi-byte white space), "
+                      "response lengths log-uniform 64 B - 64 KB, 1.25 GB per GPU (10 GB over 8), 4 per request"),
 }
 TAGS4 = ["think", "reason", "reasoning", "thought"]
 
@@ -105,8 +108,21 @@ class ClockSampler:
 # workload construction
 # ---------------------------------------------------------------------------------------------------------------
 
+class RaggedBase:
+    """Pool of ragged units (list of bytes) with the bits of the ndarray interface the CPU legs use."""
+
+    def __init__(self, units):
+        self.units = units
+        self.shape = (len(units), int(np.mean([len(u) for u in units])))
+
+    def __getitem__(self, idx):
+        return [self.units[int(i) % len(self.units)] for i in idx]
+
+
 def build_base(wl, name):
     from quorum_b200 import synth
+    if name == "cfg5":
+        return RaggedBase(synth.cfg5_units(wl["pool_bytes"], seed=1005))
     if name == "cfg2":
         return synth.cfg2_base(wl["n_base"], wl["chunks"], wl["chunk_bytes"])
     if name == "cfg3":
@@ -116,7 +132,13 @@ def build_base(wl, name):
 
 def unit_index(wl, n_units, rank):
     from quorum_b200 import synth
+    if wl["kind"] == "ragged":
+        return np.arange(n_units)
     return synth.gather_units(np.empty((wl["n_base"], 1)), n_units, seed=1000 + rank)
+
+
+def _raw(r):
+    return r if isinstance(r, (bytes, bytearray)) else r.tobytes()
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -152,13 +174,13 @@ def _ref_resp_shard(args):
     q = _REFMOD
     t0 = time.perf_counter()
     nbytes = 0
-    texts = [r.tobytes().decode() for r in rows]
+    texts = [_raw(r).decode() for r in rows]
     t0 = time.perf_counter()
     for i in range(0, len(texts), per_request):
         processed = [q.strip_thinking_tags(c, tags, hide_intermediate=True) for c in texts[i:i + per_request]]
         sep.join(processed)
     for r in rows:
-        nbytes += r.size
+        nbytes += len(_raw(r))
     return nbytes, time.perf_counter() - t0
 
 
@@ -198,6 +220,13 @@ def time_cpu(wl, name, base, cores, sample_units, repeats=1):
         ctags = c_oracle.Tags(tags)
 
         def run(shard):
+            if wl["kind"] == "ragged":
+                flat, io = synth.pack([_raw(u) for u in shard])
+                ro = np.arange(0, len(shard) + 1, wl["per_request"], dtype=np.int64)
+                if ro[-1] != len(shard):
+                    ro = np.append(ro, len(shard))
+                c_oracle.strip_concat_batch(ctags, flat, io, ro, synth.SEP_MULTIBYTE.encode(), c_oracle.FLAG_HIDE)
+                return flat.size
             flat = np.ascontiguousarray(shard).reshape(-1)
             if wl["kind"] == "stream":
                 co = np.arange(0, flat.size + 1, wl["chunk_bytes"], dtype=np.int64)
@@ -221,8 +250,8 @@ def time_cpu(wl, name, base, cores, sample_units, repeats=1):
                 best = dt if best is None else min(best, dt)
         kind = "port"
         how = f"C restatement oracle/quorum_oracle.c, {cores} threads (ctypes releases the GIL)"
-    unit_b = rows.shape[1]
-    return nbytes / best / 1e9, kind, f"{sample_units} units x {unit_b} B of the same workload; {how}"
+    unit_b = base.shape[1]
+    return nbytes / best / 1e9, kind, f"{sample_units} units x ~{unit_b} B of the same workload; {how}"
 
 
 def run_reference_arm(args, wl, name):
@@ -232,7 +261,9 @@ def run_reference_arm(args, wl, name):
         return
     cores = os.cpu_count() or 1
     base = build_base(wl, name)
-    per_core = 96 if wl["kind"] == "stream" else (2048 if wl["unit_bytes"] <= 4096 else 256)
+    per_core = 96 if wl["kind"] == "stream" else (2048 if wl.get("unit_bytes", 9000) <= 4096 else 256)
+    if wl["kind"] == "ragged":
+        per_core = min(per_core, max(4, len(base.units) // cores))
     if not cpu_reference_available():
         per_core *= 16
     sample_units = per_core * cores
@@ -265,7 +296,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))  # cfg2 = BASELINE.json configs[1]
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--units", type=int, default=0, help="override the number of units per GPU (debug)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -302,13 +333,27 @@ def main():
 
     peak, peak_src = read_peaks()
     base = build_base(wl, name)
-    n_units = wl["units"]
     unit_b = base.shape[1]
-    idx = unit_index(wl, n_units, rank)
-    base_dev = torch.from_numpy(base).to(dev)
-    idx_dev = torch.from_numpy(idx).to(dev)
-    data = base_dev.index_select(0, idx_dev).reshape(-1).contiguous()      # uint8[n_units * unit_b], device resident
-    del base_dev
+    ragged_off = None
+    if wl["kind"] == "ragged":
+        # the pool of adversarial units, rotated by rank and repeated until the per-GPU byte count is reached
+        units = base.units[rank % len(base.units):] + base.units[:rank % len(base.units)]
+        pool, poff = synth.pack(units)
+        reps = max(1, int(wl["total_bytes"] // max(1, pool.size)))
+        if args.units:
+            reps = 1
+        data = torch.from_numpy(pool.copy()).to(dev).repeat(reps).contiguous()
+        lens = torch.from_numpy(np.diff(poff)).to(dev).repeat(reps)
+        ragged_off = torch.zeros(lens.numel() + 1, dtype=torch.int64, device=dev)
+        torch.cumsum(lens, 0, out=ragged_off[1:])
+        n_units = int(lens.numel())
+    else:
+        n_units = wl["units"]
+        idx = unit_index(wl, n_units, rank)
+        base_dev = torch.from_numpy(base).to(dev)
+        idx_dev = torch.from_numpy(idx).to(dev)
+        data = base_dev.index_select(0, idx_dev).reshape(-1).contiguous()      # uint8[n_units * unit_b], device resident
+        del base_dev
     total_in = data.numel()
     table = qbatch.tag_table(synth.TAGS5)
 
@@ -332,8 +377,14 @@ def main():
         items_name = "chunks"
     else:
         pr = wl["per_request"]
+        if ragged_off is not None:
+            n_units -= n_units % pr
+            in_off = ragged_off[: n_units + 1].contiguous()
+            total_in = int(in_off[-1].item())
+            data = data[:total_in]
+        else:
+            in_off = torch.arange(0, total_in + 1, unit_b, dtype=torch.int64, device=dev)
         n_req = n_units // pr
-        in_off = torch.arange(0, total_in + 1, unit_b, dtype=torch.int64, device=dev)
         req_off = torch.arange(0, n_units + 1, pr, dtype=torch.int64, device=dev)
         sep_b = synth.SEP_MULTIBYTE.encode()
         sep = torch.frombuffer(bytearray(sep_b), dtype=torch.uint8).to(dev)
@@ -444,6 +495,8 @@ def main():
     if world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
         per_core = 64 if wl["kind"] == "stream" else (1024 if unit_b <= 4096 else 128)
+        if wl["kind"] == "ragged":
+            per_core = min(per_core, max(4, len(base.units) // cores))
         if not cpu_reference_available():
             per_core *= 16
         v, kind, sample = time_cpu(wl, name, base, cores, per_core * cores)
@@ -454,7 +507,7 @@ def main():
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic (quorum_b200/synth.py, fixed seeds)",
         "config": {"workload": wl["name"], "units_per_gpu": n_units, "unit_bytes": unit_b,
-                   "input_bytes_per_gpu": total_in, "output_bytes_per_gpu": total_out,
+                   "input_bytes_per_gpu": int(total_in), "output_bytes_per_gpu": total_out,
                    "thinking_tags": synth.TAGS5, "l2": "inputs larger than L2 (no flush needed)",
                    "sharding": f"{world} rank(s), independent units, no collective"},
         items_name + "_per_s": world * n_items / (ms * 1e-3),

@@ -64,8 +64,8 @@ __global__ void __launch_bounds__(256) tokenize_kernel(const __grid_constant__ D
             if (lane == 0) cnt[step] = 0;
             continue;
         }
-        // records of this lane's word (a 32-byte word holds at most 10 three-byte tags; more than 4 '<' is an overflow)
-        uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+        // records of this lane's word (a 32-byte word holds at most 10 three-byte tags; more than 8 '<' is an overflow)
+        uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0, r5 = 0, r6 = 0, r7 = 0;
         int n = 0;
         bool many = false;
         while (lt) {
@@ -79,6 +79,10 @@ __global__ void __launch_bounds__(256) tokenize_kernel(const __grid_constant__ D
             else if (n == 1) r1 = r;
             else if (n == 2) r2 = r;
             else if (n == 3) r3 = r;
+            else if (n == 4) r4 = r;
+            else if (n == 5) r5 = r;
+            else if (n == 6) r6 = r;
+            else if (n == 7) r7 = r;
             else many = true;
             n++;
         }
@@ -102,6 +106,10 @@ __global__ void __launch_bounds__(256) tokenize_kernel(const __grid_constant__ D
             if (n > 1) out[1] = r1;
             if (n > 2) out[2] = r2;
             if (n > 3) out[3] = r3;
+            if (n > 4) out[4] = r4;
+            if (n > 5) out[5] = r5;
+            if (n > 6) out[6] = r6;
+            if (n > 7) out[7] = r7;
         }
         if (lane == 0) cnt[step] = (uint8_t)(bad ? kRecOverflow : tot);
     }

@@ -11,11 +11,13 @@ namespace qb {
 
 // Token records written by the tokenizer pass (qb_tok.cuh), one group per absolute 1 KiB step of the flat buffer:
 //   cnt[step]  number of records (0..kRecPerStep), kRecOverflow when the step had more '<' than fit
-//   rec[step * kRecPerStep + k], in position order:
+//   rec[step * kRecPerStep + k], in position order (a walker keeps the first kRecInline of a step in registers and
+//   fetches the rest, lane per record, only for the rare step that has more):
 //     bits 0-9 position inside the step | 10-16 tag length in bytes (0 for a literal '<') | 17-18 kind
 //     (0 open tag, 1 close tag, 2 '<' that starts no complete tag) | 19-25 backreference class | 26 the tag uses a
 //     U+0130/U+0131/U+017F spelling (the walker re-reads the bytes when that matters)
-constexpr int kRecPerStep = 8;
+constexpr int kRecPerStep = 32;
+constexpr int kRecInline = 8;
 constexpr int kRecOverflow = 255;
 struct TokSrc {
     const uint8_t* cnt = nullptr;
@@ -718,14 +720,11 @@ struct StreamRunWalker {
                         live &= live - 1;
                         const int c = __shfl_sync(kFull, cnt, j);
                         const int sb = (int)(((S0 + j) << 10) - ustart);  // unit position of the step's first byte
-    #pragma unroll
-                        for (int k = 0; k < kRecPerStep; k++) {
-                            if (k >= c) break;
-                            const uint32_t r = __shfl_sync(kFull, rec_select(ra, rb, k), j);
+                        auto handle = [&](uint32_t r) {
                             const int kind = (r >> 17) & 3;
                             const int x = sb + (int)(r & 1023);
                             const int tend = x + (int)((r >> 10) & 127);
-                            if (kind == 2 || x < 0 || tend > n || x < last_tok_end) continue;  // literal '<' / cut by the unit
+                            if (kind == 2 || x < 0 || tend > n || x < last_tok_end) return;  // literal '<' / cut by the unit
                             int ex = -1;
                             if (((r >> 26) & 1) && depth == 0 && kind == 0) {  // rare: which letter uses a non-ASCII form?
                                 int cls;
@@ -734,6 +733,16 @@ struct StreamRunWalker {
                                 ex = (int)e64;
                             }
                             on_tag(x, tend, kind == 1, ex);
+                        };
+                        if (c <= kRecInline) {
+#pragma unroll
+                            for (int k = 0; k < kRecInline; k++) {
+                                if (k >= c) break;
+                                handle(__shfl_sync(kFull, rec_select(ra, rb, k), j));
+                            }
+                        } else {  // a dense step: one record per lane straight from memory
+                            const uint32_t rd = lane < c ? ts.rec[(S0 + j) * kRecPerStep + lane] : 0u;
+                            for (int k = 0; k < c; k++) handle(__shfl_sync(kFull, rd, k));
                         }
                     }
                 }
@@ -783,7 +792,8 @@ struct StreamRunWalker {
                     if (cnt > 4) qb = rp[1];
                     const int sb = (int)((sx << 10) - ustart);
                     for (int q = 0; q < cnt; q++) {
-                        const int x = sb + (int)(rec_select(qa, qb, q) & 1023);
+                        const uint32_t rq = q < kRecInline ? rec_select(qa, qb, q) : ts.rec[sx * kRecPerStep + q];
+                        const int x = sb + (int)(rq & 1023);
                         if (x >= 0 && x < c && x > p) p = x;
                     }
                 }
@@ -892,7 +902,7 @@ struct StreamRunWalker {
 // of the response one per lane.  `.strip()` then only has to look at the two ends of that list.  More than 32 runs, a
 // step whose records overflowed, or a response of 2 GiB and more set `overflow` (the caller falls back to StripWalker).
 // ------------------------------------------------------------------------------------------------------------------
-template <bool COPY>
+template <bool COPY, bool BATCH = false>  // BATCH: more than 32 kept runs are settled 32 at a time (out-of-line callers only)
 struct StripRunWalker {
     const DevTags& tg;
     const uint8_t* buf;
@@ -901,6 +911,8 @@ struct StripRunWalker {
     int lane;
     TokSrc ts;
     bool overflow = false;
+    bool many = false;  // overflow because of more than 32 kept runs (and nothing else)
+    bool wide = false;
     int64_t kept_len = 0;
     uint8_t* dst = nullptr;
     UnitDesc* desc = nullptr;  // count pass: where the trimmed runs go (copied later by the gather kernel)
@@ -923,6 +935,7 @@ struct StripRunWalker {
         __syncwarp();
         int run_s = 0, run_e = 0, nruns = 0;  // lane i keeps run i
         int state = -1, seg_start = 0;
+        bool dead = false;  // a batch could not be settled (overflow is set): ignore the rest
         int cnt = 0;
         uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
         for (int pass = 0; pass < 2; pass++) {
@@ -947,7 +960,7 @@ struct StripRunWalker {
                 const int sb0 = (int)((S0 << 10) - ustart);
                 if (pass == 0) {  // pass A: last closer per class, every lane over its own step
                     for (int k = 0; k < cnt; k++) {
-                        const uint32_t r = rec_select(ra, rb, k);
+                        const uint32_t r = k < kRecInline ? rec_select(ra, rb, k) : ts.rec[sj * kRecPerStep + k];
                         if (((r >> 17) & 3) != 1) continue;
                         const int x = sb0 + lane * 1024 + (int)(r & 1023);
                         const int tend = x + (int)((r >> 10) & 127);
@@ -959,21 +972,22 @@ struct StripRunWalker {
                         const int j = __ffs(live) - 1;
                         live &= live - 1;
                         const int c = __shfl_sync(kFull, cnt, j);
-#pragma unroll
-                        for (int k = 0; k < kRecPerStep; k++) {
-                            if (k >= c) break;
-                            const uint32_t r = __shfl_sync(kFull, rec_select(ra, rb, k), j);
+                        auto handle = [&](uint32_t r) {
                             const int kind = (r >> 17) & 3;
-                            if (kind == 2) continue;
+                            if (kind == 2 || dead) return;
                             const int x = sb0 + j * 1024 + (int)(r & 1023);
                             const int tend = x + (int)((r >> 10) & 127);
-                            if (x < 0 || tend > n) continue;
+                            if (x < 0 || tend > n) return;
                             const int cls = (r >> 19) & 127;
                             if (state < 0) {
                                 if (kind == 0 && lastclose[cls] > (unsigned long long)x) {  // live open tag
                                     if (x > seg_start) {
                                         if (lane == nruns) { run_s = seg_start; run_e = x; }
                                         nruns++;
+                                        if (BATCH && nruns == 32) {  // the lanes are full: settle this batch, start the next
+                                            if (!flush_batch(run_s, run_e, nruns, false, n, T)) dead = true;
+                                            nruns = 0;
+                                        }
                                     }
                                     state = cls;
                                 }
@@ -981,52 +995,97 @@ struct StripRunWalker {
                                 seg_start = tend;
                                 state = -1;
                             }
+                        };
+                        if (c <= kRecInline) {
+#pragma unroll
+                            for (int k = 0; k < kRecInline; k++) {
+                                if (k >= c) break;
+                                handle(__shfl_sync(kFull, rec_select(ra, rb, k), j));
+                            }
+                        } else {  // a dense step: one record per lane straight from memory
+                            const uint32_t rd = lane < c ? ts.rec[(S0 + j) * kRecPerStep + lane] : 0u;
+                            for (int k = 0; k < c; k++) handle(__shfl_sync(kFull, rd, k));
                         }
                     }
                 }
             }
             __syncwarp();
         }
+        if (dead) return;
         if (n > seg_start) {
             if (lane == nruns) { run_s = seg_start; run_e = n; }
             nruns++;
+            if (BATCH && nruns == 32) {
+                if (!flush_batch(run_s, run_e, nruns, false, n, T)) return;
+                nruns = 0;
+            }
         }
-        if (nruns > (desc ? kDescRuns : 32)) {
+        if (!BATCH && nruns > 32) {  // more runs than lanes: the caller retries with the batching variant
             overflow = true;
+            many = true;
             return;
         }
-        // .strip(): drop white space from the front of the first runs and from the back of the last ones
-        int lead = nruns;  // first run that keeps anything
-        for (int i = 0; i < nruns; i++) {
-            const int rs = __shfl_sync(kFull, run_s, i), re = __shfl_sync(kFull, run_e, i);
-            int f = -1;
-            for (int base = rs; base < re; base += 32) {
-                const int x = base + lane;
-                const bool nw = x < re && !is_white_byte(T, x, n);
-                const unsigned b = __ballot_sync(kFull, nw);
-                if (b) { f = base + __ffs(b) - 1; break; }
+        flush_batch(run_s, run_e, nruns, true, n, T);
+    }
+
+    // ---- batches of up to 32 runs (one per lane) --------------------------------------------------------------------
+    // A response with more than 32 kept runs is handled in batches: the leading `.strip()` cut is made on the first
+    // batch, the trailing one on the last, and the count pass's kept_len bounds what the copy pass writes.  The rare
+    // shapes this cannot decide locally (a whole non-final batch of white space before any text, a final batch that is
+    // all white space after earlier text) set `overflow` and go to the byte-rescanning walker.
+    int64_t flushed = 0;     // kept bytes of the batches before this one
+    bool lead_done = false;
+    int batches = 0;
+    int64_t klimit = INT64_MAX;  // copy pass: kept_len from the count pass
+
+    __device__ __forceinline__ bool flush_batch(int& run_s, int& run_e, int nruns, bool final, int n, const PtrAcc& T) {
+        int lead = 0;
+        if (!lead_done) {  // .strip(), front: drop white space from the first runs that keep anything
+            lead = nruns;
+            for (int i = 0; i < nruns; i++) {
+                const int rs = __shfl_sync(kFull, run_s, i), re = __shfl_sync(kFull, run_e, i);
+                int f = -1;
+                for (int base = rs; base < re; base += 32) {
+                    const int x = base + lane;
+                    const bool nw = x < re && !is_white_byte(T, x, n);
+                    const unsigned b = __ballot_sync(kFull, nw);
+                    if (b) { f = base + __ffs(b) - 1; break; }
+                }
+                if (f >= 0) {
+                    if (lane == i) run_s = f;
+                    lead = i;
+                    lead_done = true;
+                    break;
+                }
+                if (lane == i) run_e = run_s;  // all white
             }
-            if (f >= 0) {
-                if (lane == i) run_s = f;
-                lead = i;
-                break;
+            if (!lead_done && !final && nruns > 0) {
+                overflow = true;
+                return false;
             }
-            if (lane == i) run_e = run_s;  // all white
         }
-        for (int i = nruns - 1; i >= lead; i--) {
-            const int rs = __shfl_sync(kFull, run_s, i), re = __shfl_sync(kFull, run_e, i);
-            int l = -1;
-            for (int top = re; top > rs; top -= 32) {
-                const int x = top - 32 + lane;
-                const bool nw = x >= rs && !is_white_byte(T, x, n);
-                const unsigned b = __ballot_sync(kFull, nw);
-                if (b) { l = top - 32 + (31 - __clz(b)); break; }
+        if (final) {  // .strip(), back
+            bool found = false;
+            for (int i = nruns - 1; i >= lead; i--) {
+                const int rs = __shfl_sync(kFull, run_s, i), re = __shfl_sync(kFull, run_e, i);
+                int l = -1;
+                for (int top = re; top > rs; top -= 32) {
+                    const int x = top - 32 + lane;
+                    const bool nw = x >= rs && !is_white_byte(T, x, n);
+                    const unsigned b = __ballot_sync(kFull, nw);
+                    if (b) { l = top - 32 + (31 - __clz(b)); break; }
+                }
+                if (l >= 0) {
+                    if (lane == i) run_e = l + 1;
+                    found = true;
+                    break;
+                }
+                if (lane == i) run_e = run_s;
             }
-            if (l >= 0) {
-                if (lane == i) run_e = l + 1;
-                break;
+            if (!found && flushed > 0) {  // the text ends in an earlier batch: not decidable from here
+                overflow = true;
+                return false;
             }
-            if (lane == i) run_e = run_s;
         }
         const int mylen = lane < nruns ? run_e - run_s : 0;
         int incl = mylen;
@@ -1035,31 +1094,46 @@ struct StripRunWalker {
             int t = __shfl_up_sync(kFull, incl, d);
             if (lane >= d) incl += t;
         }
-        kept_len = __shfl_sync(kFull, incl, 31);
-        if (desc) {
-            UnitDesc& d = *desc;
-            if (lane == 0) {
-                d.nruns = nruns;
-                d.total = (int32_t)kept_len;
-                d.held_kept = 0;
-                d.depth = 0;
-                d.last_tok_end = -1;
-                d.rlast = n;
-                d.flags = 0;
-                d.pad = 0;
-            }
-            if (lane < kDescRuns) {
-                d.run_s[lane] = lane < nruns ? run_s : 0;
-                d.run_e[lane] = lane < nruns ? run_e : 0;
-            }
-        }
+        const int batch_len = __shfl_sync(kFull, incl, 31);
         if (COPY) {
             const int my_off = incl - mylen;
-            for (int i = 0; i < nruns; i++) {
-                const int rs = __shfl_sync(kFull, run_s, i), re = __shfl_sync(kFull, run_e, i), ro = __shfl_sync(kFull, my_off, i);
-                if (re > rs) warp_copy<true>(dst + ro, T.p + rs, re - rs, buf + total, lane);
+            if (batch_len <= 64 * nruns) {  // short runs: one run per lane, byte by byte
+                int64_t len = mylen;
+                if (flushed + my_off + len > klimit) len = klimit - flushed - my_off;
+                for (int64_t k = 0; k < len; k++) dst[flushed + my_off + k] = T(run_s + k);
+            } else {
+                for (int i = 0; i < nruns; i++) {
+                    const int rs = __shfl_sync(kFull, run_s, i), ro = __shfl_sync(kFull, my_off, i);
+                    int64_t len = __shfl_sync(kFull, mylen, i);
+                    if (flushed + ro + len > klimit) len = klimit - flushed - ro;  // trailing white space of the whole text
+                    if (len > 0) warp_copy<true>(dst + flushed + ro, T.p + rs, len, buf + total, lane);
+                }
             }
         }
+        if (final) {
+            wide = batches > 0 || nruns > kDescRuns;  // does not fit a descriptor: the copy kernel walks this unit again
+            kept_len = flushed + batch_len;
+            if (desc) {
+                UnitDesc& d = *desc;
+                if (lane == 0) {
+                    d.nruns = wide ? -2 : nruns;
+                    d.total = (int32_t)kept_len;
+                    d.held_kept = 0;
+                    d.depth = 0;
+                    d.last_tok_end = -1;
+                    d.rlast = n;
+                    d.flags = 0;
+                    d.pad = 0;
+                }
+                if (lane < kDescRuns) {
+                    d.run_s[lane] = lane < nruns ? run_s : 0;
+                    d.run_e[lane] = lane < nruns ? run_e : 0;
+                }
+            }
+        }
+        flushed += batch_len;
+        batches++;
+        return true;
     }
 };
 

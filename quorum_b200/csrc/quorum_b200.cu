@@ -60,6 +60,23 @@ __device__ __noinline__ void strip_copy_slow(const DevTags& tg, const uint8_t* i
     w.dst = dst;
     w.run();
 }
+// 9 or more kept runs: record-driven walk (32 runs at a time) + copy from the lanes, out of line for the same reason
+__device__ __noinline__ void strip_copy_wide(const DevTags& tg, const uint8_t* in, int64_t total, int64_t a, int64_t n,
+                                             unsigned long long* lc, int lane, TokSrc ts, int64_t kl, uint8_t* dst) {
+    StripRunWalker<true, true> w(tg, in, total, a, n, lc, lane, ts);
+    w.dst = dst;
+    w.klimit = kl;
+    w.run();
+}
+// count pass of a unit with more than 32 kept runs; returns false when even that cannot settle it
+__device__ __noinline__ bool strip_count_wide(const DevTags& tg, const uint8_t* in, int64_t total, int64_t a, int64_t n,
+                                              unsigned long long* lc, int lane, TokSrc ts, UnitDesc* desc, int64_t* kept_len) {
+    StripRunWalker<false, true> w(tg, in, total, a, n, lc, lane, ts);
+    w.desc = desc;
+    w.run();
+    *kept_len = w.kept_len;
+    return !w.overflow;
+}
 __device__ __noinline__ StreamResult stream_count_slow(const DevTags& tg, const uint8_t* bytes, int64_t total, const int64_t* co,
                                                        int64_t m, int lane, uint32_t flags, const StreamState* st_in) {
     StreamWalker<false> w(tg, bytes, total, co, m, lane, flags);
@@ -92,7 +109,7 @@ __device__ __forceinline__ void prefetch_unit_meta(const TokSrc& ts, const uint8
     else if (lane == 1) p = ts.cnt + s1;
     else if (lane == 2) p = bytes + a;
     else if (lane == 3) p = bytes + b - 1;
-    else if (s0 + (lane - 4) * 4 <= s1) p = ts.rec + (s0 + (lane - 4) * 4) * kRecPerStep;  // 4 steps of records per 128-byte line
+    else if (s0 + (lane - 4) <= s1) p = ts.rec + (s0 + (lane - 4)) * kRecPerStep;  // one step's records per 128-byte line
     if (p) asm volatile("prefetch.L1 [%0];" ::"l"(p));
 }
 
@@ -104,16 +121,8 @@ strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
-    const int64_t stride = (int64_t)gridDim.x * kWarpsPerBlock;
-    int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib;
-    int64_t a = 0, b = 0, an = 0, bn = 0;
-    if (r < n_resp) { a = in_off[r]; b = in_off[r + 1]; }
-    if (r + stride < n_resp) { an = in_off[r + stride]; bn = in_off[r + stride + 1]; }
-    for (; r < n_resp; r += stride) {
-        // offsets two units ahead (in flight while this unit is walked), record/text lines one unit ahead
-        int64_t ann = 0, bnn = 0;
-        if (r + 2 * stride < n_resp) { ann = in_off[r + 2 * stride]; bnn = in_off[r + 2 * stride + 1]; }
-        if (r + stride < n_resp) prefetch_unit_meta(ts, in, an, bn, lane);
+    for (int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib; r < n_resp; r += (int64_t)gridDim.x * kWarpsPerBlock) {
+        const int64_t a = in_off[r], b = in_off[r + 1];
         StripResult res;
         bool slow = ts.cnt == nullptr;
         if (!slow) {
@@ -124,6 +133,7 @@ strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
             res.kept_len = w.kept_len;
             res.first_pos = 0;
             slow = w.overflow;
+            if (w.many) slow = !strip_count_wide(tg, in, total, a, b - a, lastclose[wib], lane, ts, desc + r, &res.kept_len);
         }
         if (slow) {
             res = strip_count_slow(tg, in, total, a, b - a, lastclose[wib], lane);
@@ -134,7 +144,6 @@ strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
             first[r] = res.first_pos;
         }
         __syncwarp();
-        a = an; b = bn; an = ann; bn = bnn;
     }
 }
 
@@ -310,6 +319,10 @@ __device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, con
         if (lane >= d) incl += t;
     }
     const int off = dp->held_kept + incl - len;
+    if (__shfl_sync(kFull, incl, kDescRuns - 1) <= 64 * nruns) {  // short runs: one run per lane, byte by byte
+        for (int k = 0; k < len; k++) dst[off + k] = src[rs + k];
+        return;
+    }
     for (int i = 0; i < nruns; i++) {  // get every source line of every run moving before the first copy waits on one
         const int s_i = __shfl_sync(kFull, rs, i), l_i = __shfl_sync(kFull, len, i);
         const uint8_t* a = src + s_i;
@@ -328,7 +341,8 @@ __global__ void __launch_bounds__(kThreads, 5)
 strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
                   int64_t n_resp, const int64_t* __restrict__ klen, const int64_t* __restrict__ first,
                   const int64_t* __restrict__ dst, int hide, const uint8_t* __restrict__ sep, int32_t sep_len,
-                  uint8_t* __restrict__ out, int64_t* __restrict__ resp_out_len, const UnitDesc* __restrict__ desc) {
+                  uint8_t* __restrict__ out, int64_t* __restrict__ resp_out_len, const UnitDesc* __restrict__ desc,
+                  TokSrc ts) {
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
@@ -347,8 +361,11 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
         if (!hide) {
             warp_copy<true>(out + d, in + a, b - a, in + total, lane);
         } else if (kl > 0) {
-            if (desc && desc[r].nruns >= 0) {
+            const int nr = desc ? desc[r].nruns : -1;
+            if (nr >= 0) {
                 gather_unit(desc + r, in + a, out + d, in + total, lane);
+            } else if (nr == -2) {  // 9..32 kept runs: walk the records again and copy from the lanes
+                strip_copy_wide(tg, in, total, a, b - a, lastclose[wib], lane, ts, kl, out + d);
             } else {
                 strip_copy_slow(tg, in, total, a, b - a, lastclose[wib], lane, first[r], kl, out + d);
             }
@@ -634,7 +651,7 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     if (n_resp > 0) {
         strip_copy_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, dst,
                                                                     hide, sep, sep_len, out_bytes, resp_out_len,
-                                                                    (hide && ts.cnt) ? desc : nullptr);
+                                                                    (hide && ts.cnt) ? desc : nullptr, ts);
         LAUNCHED();
     }
     CUDA_TRY(cudaGetLastError());

@@ -16,7 +16,7 @@ namespace qb {
 //     bits 0-9 position inside the step | 10-16 tag length in bytes (0 for a literal '<') | 17-18 kind
 //     (0 open tag, 1 close tag, 2 '<' that starts no complete tag) | 19-25 backreference class | 26 the tag uses a
 //     U+0130/U+0131/U+017F spelling (the walker re-reads the bytes when that matters)
-constexpr int kRecPerStep = 32;
+constexpr int kRecPerStep = 48;
 constexpr int kRecInline = 8;
 constexpr int kRecOverflow = 255;
 struct TokSrc {
@@ -740,9 +740,11 @@ struct StreamRunWalker {
                                 if (k >= c) break;
                                 handle(__shfl_sync(kFull, rec_select(ra, rb, k), j));
                             }
-                        } else {  // a dense step: one record per lane straight from memory
-                            const uint32_t rd = lane < c ? ts.rec[(S0 + j) * kRecPerStep + lane] : 0u;
-                            for (int k = 0; k < c; k++) handle(__shfl_sync(kFull, rd, k));
+                        } else {  // a dense step: one record per lane straight from memory, 32 at a time
+                            for (int k0 = 0; k0 < c; k0 += 32) {
+                                const uint32_t rd = k0 + lane < c ? ts.rec[(S0 + j) * kRecPerStep + k0 + lane] : 0u;
+                                for (int k = 0; k < 32 && k0 + k < c; k++) handle(__shfl_sync(kFull, rd, k));
+                            }
                         }
                     }
                 }
@@ -1002,9 +1004,47 @@ struct StripRunWalker {
                                 if (k >= c) break;
                                 handle(__shfl_sync(kFull, rec_select(ra, rb, k), j));
                             }
-                        } else {  // a dense step: one record per lane straight from memory
-                            const uint32_t rd = lane < c ? ts.rec[(S0 + j) * kRecPerStep + lane] : 0u;
-                            for (int k = 0; k < c; k++) handle(__shfl_sync(kFull, rd, k));
+                        } else {  // a dense step: one record per lane straight from memory, 32 at a time.
+                            // Every lane decodes its own record and looks up liveness; the automaton then only visits the
+                            // records that change its state (ballot + find-first-set), not every record.
+                            for (int k0 = 0; k0 < c && !dead; k0 += 32) {
+                                const uint32_t r = k0 + lane < c ? ts.rec[(S0 + j) * kRecPerStep + k0 + lane] : (2u << 17);
+                                const int kind = (r >> 17) & 3;
+                                const int x = sb0 + j * 1024 + (int)(r & 1023);
+                                const int tend = x + (int)((r >> 10) & 127);
+                                const int cls = (r >> 19) & 127;
+                                const bool valid = kind != 2 && x >= 0 && tend <= n;
+                                const bool live = valid && kind == 0 && lastclose[cls] > (unsigned long long)x;
+                                const unsigned open_m = __ballot_sync(kFull, live);
+                                int pos = 0;
+                                while (pos < 32) {
+                                    const unsigned from = 0xffffffffu << pos;
+                                    if (state < 0) {
+                                        const unsigned mm = open_m & from;
+                                        if (!mm) break;
+                                        const int i = __ffs(mm) - 1;
+                                        const int xi = __shfl_sync(kFull, x, i);
+                                        if (xi > seg_start) {
+                                            if (lane == nruns) { run_s = seg_start; run_e = xi; }
+                                            nruns++;
+                                            if (BATCH && nruns == 32) {
+                                                if (!flush_batch(run_s, run_e, nruns, false, n, T)) dead = true;
+                                                nruns = 0;
+                                            }
+                                        }
+                                        state = __shfl_sync(kFull, cls, i);
+                                        pos = i + 1;
+                                    } else {
+                                        const unsigned mm = __ballot_sync(kFull, valid && kind == 1 && cls == state) & from;
+                                        if (!mm) break;
+                                        const int i = __ffs(mm) - 1;
+                                        seg_start = __shfl_sync(kFull, tend, i);
+                                        state = -1;
+                                        pos = i + 1;
+                                    }
+                                    if (dead) break;
+                                }
+                            }
                         }
                     }
                 }
@@ -1030,10 +1070,11 @@ struct StripRunWalker {
 
     // ---- batches of up to 32 runs (one per lane) --------------------------------------------------------------------
     // A response with more than 32 kept runs is handled in batches: the leading `.strip()` cut is made on the first
-    // batch, the trailing one on the last, and the count pass's kept_len bounds what the copy pass writes.  The rare
-    // shapes this cannot decide locally (a whole non-final batch of white space before any text, a final batch that is
-    // all white space after earlier text) set `overflow` and go to the byte-rescanning walker.
+    // batch that has text, every batch remembers where its text ends (so a white-space-only tail of later batches is
+    // cut correctly), and the count pass's kept_len bounds what the copy pass writes.  A whole non-final batch of white
+    // space before any text sets `overflow` (byte-rescanning walker).
     int64_t flushed = 0;     // kept bytes of the batches before this one
+    int64_t text_end = 0;    // kept length up to the last non-white byte seen in the batches before this one
     bool lead_done = false;
     int batches = 0;
     int64_t klimit = INT64_MAX;  // copy pass: kept_len from the count pass
@@ -1064,8 +1105,11 @@ struct StripRunWalker {
                 return false;
             }
         }
-        if (final) {  // .strip(), back
-            bool found = false;
+        // .strip(), back: where does the text of this batch end?  The final batch is cut there; for an earlier batch the
+        // answer is remembered in case every later batch turns out to be white space only.
+        bool found = false;
+        int end_run = -1, end_pos = 0;
+        if (lead_done) {
             for (int i = nruns - 1; i >= lead; i--) {
                 const int rs = __shfl_sync(kFull, run_s, i), re = __shfl_sync(kFull, run_e, i);
                 int l = -1;
@@ -1076,15 +1120,19 @@ struct StripRunWalker {
                     if (b) { l = top - 32 + (31 - __clz(b)); break; }
                 }
                 if (l >= 0) {
-                    if (lane == i) run_e = l + 1;
                     found = true;
+                    end_run = i;
+                    end_pos = l + 1;
                     break;
                 }
-                if (lane == i) run_e = run_s;
             }
-            if (!found && flushed > 0) {  // the text ends in an earlier batch: not decidable from here
-                overflow = true;
-                return false;
+        }
+        if (final) {
+            if (found) {
+                if (lane == end_run) run_e = end_pos;
+                if (lane > end_run) run_e = run_s;
+            } else {
+                run_e = run_s;  // nothing but white space in this batch
             }
         }
         const int mylen = lane < nruns ? run_e - run_s : 0;
@@ -1095,6 +1143,10 @@ struct StripRunWalker {
             if (lane >= d) incl += t;
         }
         const int batch_len = __shfl_sync(kFull, incl, 31);
+        if (found && !final) {  // kept length if the text ended inside this batch
+            const int before = __shfl_sync(kFull, incl - mylen, end_run), rs_e = __shfl_sync(kFull, run_s, end_run);
+            text_end = flushed + before + (end_pos - rs_e);
+        }
         if (COPY) {
             const int my_off = incl - mylen;
             if (batch_len <= 64 * nruns) {  // short runs: one run per lane, byte by byte
@@ -1112,7 +1164,7 @@ struct StripRunWalker {
         }
         if (final) {
             wide = batches > 0 || nruns > kDescRuns;  // does not fit a descriptor: the copy kernel walks this unit again
-            kept_len = flushed + batch_len;
+            kept_len = found ? flushed + batch_len : text_end;  // all white at the end: the text ended in an earlier batch
             if (desc) {
                 UnitDesc& d = *desc;
                 if (lane == 0) {

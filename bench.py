@@ -53,7 +53,7 @@ def read_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms while the timed regions (device and end to end) run."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -66,7 +66,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                          "-lms", "50", "-i", str(self.gpu)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -294,7 +294,7 @@ def run_reference_arm(args, wl, name):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))  # cfg2 = BASELINE.json configs[1]
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
@@ -424,7 +424,6 @@ def main():
     torch.cuda.synchronize()
     launches = quorum_b200.launch_count() - l0
     barrier()
-    clocks = sampler.stop()
     ms = ev0.elapsed_time(ev1) / args.steps
     if world > 1:
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
@@ -468,6 +467,7 @@ def main():
         e2e = {"value": world * total_in / dt / 1e9, "unit": "GB/s", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": dt * 1e3}
         del h_data, sess
+    clocks = sampler.stop()
 
     if rank != 0:
         if world > 1:

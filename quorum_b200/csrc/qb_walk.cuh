@@ -762,13 +762,24 @@ struct StreamRunWalker {
         int R_last = 0, P_last = 0;
         bool have_last = false;
         if (COPY && lane == 0) out_chunk_off[chunk0] = out_base;
-        // every lane gets its own copy of the (at most kDescRuns) runs: the boundary loop then needs no shuffles
-        int rsv[kDescRuns], rev[kDescRuns];
+        // every lane gets its own copy of the (at most kDescRuns) run starts: run_of(x) = number of runs that start
+        // at or before x, found with kDescRuns compares; the run's data then comes from the owning lane (shuffle)
+        int rsv[kDescRuns];
 #pragma unroll
         for (int i = 0; i < kDescRuns; i++) {
             rsv[i] = __shfl_sync(kFull, run_s, i);
-            rev[i] = __shfl_sync(kFull, run_e, i);
-            if (i >= nruns) rsv[i] = rev[i] = 0;
+            if (i >= nruns) rsv[i] = INT32_MAX;
+        }
+        int run_before = 0;  // lane i: kept bytes in runs 0..i-1 (exclusive prefix of run lengths)
+        {
+            const int len = lane < nruns ? run_e - run_s : 0;
+            int incl = len;
+#pragma unroll
+            for (int d = 1; d < kDescRuns; d <<= 1) {
+                int t = __shfl_up_sync(kFull, incl, d);
+                if (lane >= d) incl += t;
+            }
+            run_before = incl - len;
         }
         const int64_t kb0 = COPY ? 1 : m;
         int64_t cnext = kb0 + lane <= m ? co[kb0 + lane] : 0;  // boundaries are fetched one batch ahead
@@ -802,14 +813,19 @@ struct StreamRunWalker {
             }
             // released-candidate bytes before c: carried literal bytes + overlap of [0, c) with the runs; and is the
             // '<' at p kept text (inside a run)?  One uniform loop over the runs for both.
-            int P = held_kept;
-            bool p_kept = false;
+            int kc = 0, kp = 0;  // runs starting at or before c-1 / at or before p
 #pragma unroll
             for (int i = 0; i < kDescRuns; i++) {
-                const int hi = min(c, rev[i]);
-                P += max(hi - rsv[i], 0);
-                p_kept |= (p >= rsv[i] && p < rev[i]);
+                kc += rsv[i] < c;
+                kp += rsv[i] <= p;
             }
+            // the last of those runs decides: everything before it is kept in full, it contributes min(c, end) - start
+            const int ic = kc > 0 ? kc - 1 : 0, ip = kp > 0 ? kp - 1 : 0;
+            const int s_c = __shfl_sync(kFull, run_s, ic), e_c = __shfl_sync(kFull, run_e, ic), b_c = __shfl_sync(kFull, run_before, ic);
+            const int e_p = __shfl_sync(kFull, run_e, ip);
+            int P = held_kept;
+            if (kc > 0) P += b_c + (min(c, e_c) - s_c);
+            const bool p_kept = kp > 0 && p < e_p;
             int R = c;
             const bool found_lt = p >= 0;
             if (found_lt && p_kept && c - p <= kHeldMax && tg.hold_enabled && is_tag_prefix(tg, T, p, c, true, false)) {

@@ -39,6 +39,7 @@ extern "C" {
 #define QB200_HIDE 1u        /* strip_concat: apply the filter + .strip()  (hide_final_think, oai_proxy.py:134-139) */
 #define QB200_STREAM_JOIN 2u /* strip_concat: streaming-final join, drop inputs that are empty BEFORE the filter (oai_proxy.py:760-764) */
 #define QB200_FLUSH 4u       /* stream_feed: apply ThinkingTagFilter.flush() after the last chunk (oai_proxy.py:739, 352-371) */
+#define QB200_SKIP_EMPTY 16u /* sse_frame: items with empty content produce no event (`if safe_text`, oai_proxy.py:625-628) */
 #define QB200_CHAIN 8u       /* stream_feed: this call is one slice of a larger batch, see qb200_stream_feed_batch */
 
 typedef struct qb200_tags qb200_tags; /* opaque, host-side */
@@ -127,6 +128,23 @@ int qb200_stream_feed_batch_noalloc(const qb200_tags *tags, const uint8_t *chunk
 
 /* ThinkingTagFilter.flush for n streams without feeding (oai_proxy.py:352-371): drops the held partial, keeps depth. */
 int qb200_stream_flush_batch(qb200_stream_state *state, int64_t n_streams, void *stream);
+
+/* SSE output framing of filtered deltas (SURVEY.md section 8, row f1 - the component right after the filter).
+ *   replaces  f"data: {json.dumps(stream_event)}\n\n".encode()      oai_proxy.py:629-652 (per-backend events)
+ *             f"data: {json.dumps(final_event)}\n\n".encode()       oai_proxy.py:847-862 (final event)
+ * Everything in the event except delta.content is constant per backend, so the host renders, once, one PREFIX per
+ * backend (`data: {"id": "chatcmpl-parallel-<i>", ..., "delta": {"content": "`) and one SUFFIX (`"}, "finish_reason": null}]}\n\n`)
+ * with json.dumps; item k becomes prefix[item_prefix[k]] + json_escape(content_k) + suffix, where json_escape is CPython's
+ * ensure_ascii string encoder (short forms for " \ \n \r \t \b \f, \u00xx for the other C0 controls and 0x7F, \uXXXX for
+ * every non-ASCII code point, surrogate pairs above U+FFFF, lower-case hex).  With QB200_SKIP_EMPTY an item whose content
+ * is empty produces no bytes.  item_prefix may be NULL (all items use prefix 0).  All pointers are device pointers;
+ * event k is out_bytes[out_off[k] .. out_off[k+1]).  out_capacity must be >= 6 * content bytes + n_items * (longest
+ * prefix + suffix_len). */
+size_t qb200_sse_frame_scratch_bytes(int64_t n_items);
+int qb200_sse_frame_batch(const uint8_t *in_bytes, const int64_t *in_off, int64_t n_items, const int32_t *item_prefix,
+                          const uint8_t *prefix_bytes, const int64_t *prefix_off, int32_t n_prefix, const uint8_t *suffix,
+                          int32_t suffix_len, uint32_t flags, uint8_t *out_bytes, int64_t out_capacity, int64_t *out_off,
+                          void *scratch, size_t scratch_bytes, void *stream);
 
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 int64_t qb200_launch_count(void);

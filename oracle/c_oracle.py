@@ -141,3 +141,38 @@ def stream_feed_batch(tags: Tags, chunk_bytes: np.ndarray, chunk_off: np.ndarray
     if rc != 0:
         raise RuntimeError(f"qo_stream_feed_batch failed: {rc}")
     return out[: int(oco[-1])], oco, state_out[:n_streams]
+
+
+def json_escape(content: bytes) -> bytes:
+    """Body of json.dumps(str) (ensure_ascii) for UTF-8 bytes, via the C restatement."""
+    L = lib()
+    if not hasattr(L, "_qo_json_ready"):
+        L.qo_json_escape.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
+        L.qo_json_escape.restype = ctypes.c_int64
+        L.qo_sse_frame_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p,
+                                         ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int, ctypes.c_void_p,
+                                         ctypes.c_int64, ctypes.c_void_p]
+        L.qo_sse_frame_batch.restype = ctypes.c_int
+        L._qo_json_ready = True
+    out = ctypes.create_string_buffer(6 * len(content) + 1)
+    n = L.qo_json_escape(content, len(content), out)
+    return out.raw[:n]
+
+
+def sse_frame_batch(in_bytes: np.ndarray, in_off: np.ndarray, item_prefix: Optional[np.ndarray], prefixes: Sequence[bytes],
+                    suffix: bytes, skip_empty: bool):
+    """Returns (out_bytes[:total], out_off[n+1])."""
+    json_escape(b"")  # binds the functions
+    n = len(in_off) - 1
+    pb = np.frombuffer(b"".join(prefixes) + b"\0", dtype=np.uint8)
+    po = np.zeros(len(prefixes) + 1, dtype=np.int64)
+    po[1:] = np.cumsum([len(p) for p in prefixes])
+    cap = 6 * int(in_off[-1]) + n * (max(len(p) for p in prefixes) + len(suffix)) + 16
+    out = np.empty(cap, dtype=np.uint8)
+    out_off = np.empty(n + 1, dtype=np.int64)
+    sa = np.frombuffer(suffix + b"\0", dtype=np.uint8)
+    rc = lib().qo_sse_frame_batch(_ptr(in_bytes), _ptr(in_off), n, _ptr(item_prefix), _ptr(pb), _ptr(po), _ptr(sa), len(suffix),
+                                  int(skip_empty), _ptr(out), cap, _ptr(out_off))
+    if rc != 0:
+        raise RuntimeError(f"qo_sse_frame_batch failed: {rc}")
+    return out[: int(out_off[-1])], out_off

@@ -336,5 +336,75 @@ int qo_stream_feed_batch(const qo_tags *t, const uint8_t *chunk_bytes, const int
     return 0;
 }
 
+/* CPython json.dumps(str) body (ensure_ascii=True) on UTF-8 bytes, without the surrounding quotes.
+ * Restates json.encoder.py_encode_basestring_ascii, the string encoder behind the reference's
+ * f"data: {json.dumps(stream_event)}\n\n" (oai_proxy.py:646, 860).  out must hold 6*n bytes.  Returns length. */
+int64_t qo_json_escape(const uint8_t *in, int64_t n, uint8_t *out) {
+    static const char hex[] = "0123456789abcdef";
+    int64_t o = 0;
+    for (int64_t i = 0; i < n;) {
+        uint32_t c = in[i];
+        if (c < 0x80) {
+            i++;
+            const char *sh = c == '"' ? "\\\"" : c == '\\' ? "\\\\" : c == '\n' ? "\\n" : c == '\r' ? "\\r" : c == '\t' ? "\\t"
+                           : c == '\b' ? "\\b" : c == '\f' ? "\\f" : NULL;
+            if (sh) { out[o++] = (uint8_t)sh[0]; out[o++] = (uint8_t)sh[1]; continue; }
+            if (c >= 0x20 && c < 0x7F) { out[o++] = (uint8_t)c; continue; }
+        } else if (c < 0xE0) {
+            c = ((c & 0x1F) << 6) | (i + 1 < n ? (in[i + 1] & 0x3F) : 0);
+            i += 2;
+        } else if (c < 0xF0) {
+            c = ((c & 0x0F) << 12) | ((i + 1 < n ? (in[i + 1] & 0x3F) : 0) << 6) | (i + 2 < n ? (in[i + 2] & 0x3F) : 0);
+            i += 3;
+        } else {
+            c = ((c & 0x07) << 18) | ((i + 1 < n ? (in[i + 1] & 0x3F) : 0) << 12) | ((i + 2 < n ? (in[i + 2] & 0x3F) : 0) << 6) |
+                (i + 3 < n ? (in[i + 3] & 0x3F) : 0);
+            i += 4;
+        }
+        uint32_t units[2];
+        int nu = 1;
+        if (c >= 0x10000) {
+            c -= 0x10000;
+            units[0] = 0xD800 + ((c >> 10) & 0x3FF);
+            units[1] = 0xDC00 + (c & 0x3FF);
+            nu = 2;
+        } else {
+            units[0] = c;
+        }
+        for (int k = 0; k < nu; k++) {
+            out[o++] = '\\';
+            out[o++] = 'u';
+            out[o++] = (uint8_t)hex[(units[k] >> 12) & 15];
+            out[o++] = (uint8_t)hex[(units[k] >> 8) & 15];
+            out[o++] = (uint8_t)hex[(units[k] >> 4) & 15];
+            out[o++] = (uint8_t)hex[units[k] & 15];
+        }
+    }
+    return o;
+}
+
+/* SSE framing of a batch: item k -> prefix[item_prefix[k]] + escape(content_k) + suffix (host memory twin of
+ * qb200_sse_frame_batch).  skip_empty: items with empty content produce nothing (oai_proxy.py:625-628). */
+int qo_sse_frame_batch(const uint8_t *in_bytes, const int64_t *in_off, int64_t n_items, const int32_t *item_prefix,
+                       const uint8_t *prefix_bytes, const int64_t *prefix_off, const uint8_t *suffix, int32_t suffix_len,
+                       int skip_empty, uint8_t *out_bytes, int64_t out_capacity, int64_t *out_off) {
+    int64_t o = 0;
+    for (int64_t k = 0; k < n_items; k++) {
+        out_off[k] = o;
+        int64_t len = in_off[k + 1] - in_off[k];
+        if (skip_empty && len == 0) continue;
+        int p = item_prefix ? item_prefix[k] : 0;
+        int64_t pl = prefix_off[p + 1] - prefix_off[p];
+        if (o + pl + 6 * len + suffix_len > out_capacity) return -10;
+        memcpy(out_bytes + o, prefix_bytes + prefix_off[p], (size_t)pl);
+        o += pl;
+        o += qo_json_escape(in_bytes + in_off[k], len, out_bytes + o);
+        memcpy(out_bytes + o, suffix, (size_t)suffix_len);
+        o += suffix_len;
+    }
+    out_off[n_items] = o;
+    return 0;
+}
+
 int qo_sizeof_tags(void) { return (int)sizeof(qo_tags); }
 int qo_sizeof_state(void) { return (int)sizeof(qo_stream_state); }

@@ -8,7 +8,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libquorum_b200.so")
 
-QB200_HIDE, QB200_STREAM_JOIN, QB200_FLUSH, QB200_CHAIN = 1, 2, 4, 8
+QB200_HIDE, QB200_STREAM_JOIN, QB200_FLUSH, QB200_CHAIN, QB200_SKIP_EMPTY = 1, 2, 4, 8, 16
 HELD_MAX = 23
 STATE_BYTES = 32
 
@@ -16,6 +16,7 @@ EXPORTS = [
     "qb200_last_error", "qb200_tags_create", "qb200_tags_destroy", "qb200_strip_concat_scratch_bytes",
     "qb200_strip_concat_batch", "qb200_stream_feed_scratch_bytes", "qb200_stream_feed_batch",
     "qb200_stream_flush_batch", "qb200_launch_count", "qb200_stream_feed_batch_noalloc",
+    "qb200_sse_frame_scratch_bytes", "qb200_sse_frame_batch",
 ]
 NOALLOC_MAX_STREAMS = 65536
 
@@ -52,6 +53,10 @@ def lib() -> ctypes.CDLL:
     L.qb200_stream_feed_batch.argtypes = [vp, vp, vp, i64, vp, i64, vp, vp, u32, vp, i64, vp, vp, sz, vp]
     L.qb200_stream_feed_batch_noalloc.restype = ctypes.c_int
     L.qb200_stream_feed_batch_noalloc.argtypes = [vp, vp, vp, i64, vp, i64, vp, vp, u32, vp, i64, vp, vp]
+    L.qb200_sse_frame_scratch_bytes.restype = sz
+    L.qb200_sse_frame_scratch_bytes.argtypes = [i64]
+    L.qb200_sse_frame_batch.restype = ctypes.c_int
+    L.qb200_sse_frame_batch.argtypes = [vp, vp, i64, vp, vp, vp, i32, vp, i32, u32, vp, i64, vp, vp, sz, vp]
     L.qb200_stream_flush_batch.restype = ctypes.c_int
     L.qb200_stream_flush_batch.argtypes = [vp, i64, vp]
     L.qb200_launch_count.restype = i64

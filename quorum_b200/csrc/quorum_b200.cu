@@ -17,6 +17,7 @@
 #include "qb_walk.cuh"
 #include "qb_tile.cuh"
 #include "qb_tok.cuh"
+#include "qb_sse.cuh"
 #include <stdlib.h>
 
 using namespace qb;
@@ -864,6 +865,44 @@ int qb200_stream_feed_batch_noalloc(const qb200_tags* tags, const uint8_t* chunk
     return stream_feed_general(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, state_in, state_out, flags,
                                out_bytes, out_capacity, out_chunk_off, scratch, (size_t)QB200_NOALLOC_SCRATCH_BYTES_,
                                (cudaStream_t)stream_);
+}
+
+size_t qb200_sse_frame_scratch_bytes(int64_t n_items) {
+    if (n_items < 0) n_items = 0;
+    return align256((size_t)(n_items + 2) * 8) + align256((size_t)(n_items / kScanSlice + 4) * 8) + 256;
+}
+
+int qb200_sse_frame_batch(const uint8_t* in_bytes, const int64_t* in_off, int64_t n_items, const int32_t* item_prefix,
+                          const uint8_t* prefix_bytes, const int64_t* prefix_off, int32_t n_prefix, const uint8_t* suffix,
+                          int32_t suffix_len, uint32_t flags, uint8_t* out_bytes, int64_t out_capacity, int64_t* out_off,
+                          void* scratch, size_t scratch_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!in_off || !out_off || !prefix_off || n_items < 0 || n_prefix < 1 || suffix_len < 0 || out_capacity < 0 ||
+        (suffix_len > 0 && !suffix))
+        return fail(QB200_EINVAL, "sse_frame_batch: bad argument");
+    if (scratch_bytes < qb200_sse_frame_scratch_bytes(n_items) || !scratch)
+        return fail(QB200_ESCRATCH, "sse_frame_batch: scratch too small");
+    int dev_count = 0;
+    CUDA_TRY(cudaGetDeviceCount(&dev_count));
+    if (n_items == 0) {
+        set_i64_kernel<<<1, 1, 0, stream>>>(out_off, 0);
+        LAUNCHED();
+        CUDA_TRY(cudaGetLastError());
+        return QB200_OK;
+    }
+    int64_t* lens = (int64_t*)scratch;
+    int64_t* partial = (int64_t*)((uint8_t*)scratch + align256((size_t)(n_items + 2) * 8));
+    int64_t blocks = (n_items + 7) / 8;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    sse_count_kernel<<<(unsigned)blocks, 256, 0, stream>>>(in_bytes, in_off, n_items, item_prefix, prefix_off, suffix_len, flags,
+                                                          lens);
+    LAUNCHED();
+    launch_scan(lens, n_items, out_off, partial, stream);
+    sse_write_kernel<<<(unsigned)blocks, 256, 0, stream>>>(in_bytes, in_off, n_items, item_prefix, prefix_bytes, prefix_off, suffix,
+                                                          suffix_len, out_off, out_bytes);
+    LAUNCHED();
+    CUDA_TRY(cudaGetLastError());
+    return QB200_OK;
 }
 
 int qb200_stream_flush_batch(qb200_stream_state* state, int64_t n_streams, void* stream_) {

@@ -39,11 +39,21 @@ __device__ __forceinline__ uint32_t rec_select(const uint4& a, const uint4& b, i
 // the unit in unit coordinates plus the few scalars of the automaton's final state.  nruns < 0: the unit did not fit
 // (more than kDescRuns runs, overflowed record slots, 2 GiB and more) and is redone by the byte-rescanning walkers.
 constexpr int kDescRuns = 8;
+constexpr int kDescHolds = 4;
 struct UnitDesc {
-    int32_t nruns, total, held_kept, depth, last_tok_end, rlast, flags, pad;  // flags: 1 held '<' unconsumed, 2 final run open-ended
+    int32_t nruns, total, held_kept, depth, last_tok_end, rlast, flags, held_len;  // flags: 1 held '<' unconsumed, 2 final run open-ended, 4 carried bytes are literal text
     int32_t run_s[kDescRuns], run_e[kDescRuns];
 };
 static_assert(sizeof(UnitDesc) == 96, "descriptor layout");
+// What a stream adds for the per-chunk offsets (stream_offsets_kernel reads only descriptors, never text or records)
+struct StreamDesc : UnitDesc {
+    int64_t ustart;  // flat position of the stream's first byte in this call
+    int64_t pad;
+    // '<' that stay text at depth 0 and can be held back by a feed boundary: a boundary c with hold_x < c <= hold_e
+    // releases only the bytes before hold_x (unused slots never match)
+    int32_t hold_x[kDescHolds], hold_e[kDescHolds];
+};
+static_assert(sizeof(StreamDesc) == 144, "descriptor layout");
 
 // true when any step touched by the unit [ustart, ustart+n) overflowed its record slots (then the unit is walked
 // the slow way, straight from its bytes)
@@ -560,10 +570,25 @@ struct StreamWalker {
 // The count pass is phase 1 plus the last boundary.  Positions are unit-relative int32 (units of 2 GiB and more take
 // the fallback).
 // ------------------------------------------------------------------------------------------------------------------
-template <int MODE>  // 0: walk + released total + descriptor;  1: per-chunk offsets + carried state from a descriptor
+// The largest e in [c, min(x + kHeldMax, n)] such that text[x, e) is a proper prefix of an open tag (hold-back test,
+// oai_proxy.py:311-323), or c - 1 when text[x, c) is none.  The test is monotone in e.  Out of line: rare.
+template <class A>
+__device__ __noinline__ int hold_interval_end(const DevTags& tg, const A acc, int x, int c, int n) {
+    if (!is_tag_prefix(tg, acc, x, c, true, false)) return c - 1;
+    int lo = c, hi = min(x + kHeldMax, n);
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (is_tag_prefix(tg, acc, x, mid, true, false)) lo = mid;
+        else hi = mid - 1;
+    }
+    return lo;
+}
+
+// MODE 0: walk + released total + descriptor (count kernel);  2: carried literal bytes + carried state from the
+// descriptor (finish kernel; the per-chunk offsets come from stream_offsets_kernel)
+template <int MODE>
 struct StreamRunWalker {
-    static constexpr bool COPY = MODE == 1;
-    UnitDesc* desc = nullptr;
+    StreamDesc* desc = nullptr;
     const DevTags& tg;
     const uint8_t* buf;
     int64_t total;
@@ -574,9 +599,6 @@ struct StreamRunWalker {
     TokSrc ts;
     bool overflow = false;
     uint8_t* dst = nullptr;
-    int64_t out_base = 0;
-    int64_t* out_chunk_off = nullptr;
-    int64_t chunk0 = 0;
 
     __device__ StreamRunWalker(const DevTags& tg_, const uint8_t* buf_, int64_t total_, const int64_t* co_, int64_t m_, int lane_,
                                uint32_t flags_, TokSrc ts_)
@@ -594,7 +616,7 @@ struct StreamRunWalker {
         }
         StreamResult res{0};
         if (m <= 0) {  // nothing fed: state passes through
-            if (COPY && st_out && lane == 0) {
+            if (MODE != 0 && st_out && lane == 0) {
                 if (flags & 4u) si.held_len = 0;
                 for (int i = si.held_len; i < kHeldMax; i++) si.held[i] = 0;
                 si.tail_len = -1;
@@ -648,8 +670,8 @@ struct StreamRunWalker {
                 cum += e - seg_start;
             }
         };
-        auto on_tag = [&](int x, int tend, bool is_close, int ex) {
-            if (!recognised(is_close, x, tend, ex)) return;
+        auto on_tag = [&](int x, int tend, bool is_close, int ex) -> bool {
+            if (!recognised(is_close, x, tend, ex)) return false;
             if (depth == 0) {
                 close_run(x);
                 depth = 1;
@@ -658,11 +680,29 @@ struct StreamRunWalker {
                 if (depth == 0) seg_start = tend;
             }
             last_tok_end = tend;
+            return true;
+        };
+        // A '<' at x that stays text at depth 0.  The reference holds it back at a feed boundary c when text[x, c) could
+        // still grow into an open tag (oai_proxy.py:311-323): such a boundary releases only the bytes before x.  The
+        // prefix test is monotone in c, so the boundaries concerned are the ones in (x, e] for one e; candidates with no
+        // boundary in their interval are dropped here, the others go to the descriptor (lane i keeps candidate i).
+        int nh = 0, hold_x = INT32_MAX, hold_e = INT32_MIN;
+        auto hold_candidate = [&](const auto& acc, int x) {
+            if (!tg.hold_enabled) return;
+            const int c = (int)(co[first_boundary_after(x)] - ustart);
+            if (c - x > kHeldMax) return;
+            const int e = hold_interval_end(tg, acc, x, c, n);
+            if (e < c) return;
+            if (lane == nh) {
+                hold_x = x;
+                hold_e = e;
+            }
+            nh++;
         };
 
         bool has_final = false;
-        if (MODE == 1) {  // everything phase 1 would find out is in the descriptor
-            const UnitDesc& d = *desc;
+        if (MODE != 0) {  // everything phase 1 would find out is in the descriptor
+            const StreamDesc& d = *desc;
             nruns = d.nruns;
             held_kept = (d.flags & 4) ? h : 0;
             depth = d.depth;
@@ -689,7 +729,10 @@ struct StreamRunWalker {
                     last_tok_end = seg_start = (int)tend;
                 } else {
                     held_unconsumed = true;
-                    if (depth == 0) held_kept = h;
+                    if (depth == 0) {
+                        held_kept = h;
+                        hold_candidate(A, -h);
+                    }
                 }
             }
             cum = held_kept;
@@ -724,15 +767,19 @@ struct StreamRunWalker {
                             const int kind = (r >> 17) & 3;
                             const int x = sb + (int)(r & 1023);
                             const int tend = x + (int)((r >> 10) & 127);
-                            if (kind == 2 || x < 0 || tend > n || x < last_tok_end) return;  // literal '<' / cut by the unit
-                            int ex = -1;
-                            if (((r >> 26) & 1) && depth == 0 && kind == 0) {  // rare: which letter uses a non-ASCII form?
-                                int cls;
-                                int64_t e64;
-                                match_tag(tg, T, x, n, false, cls, e64);
-                                ex = (int)e64;
+                            if (x < 0 || x >= n || x < last_tok_end) return;  // another unit's / inside a consumed tag
+                            bool took = false;
+                            if (kind != 2 && tend <= n) {  // a complete tag inside the unit
+                                int ex = -1;
+                                if (((r >> 26) & 1) && depth == 0 && kind == 0) {  // rare: which letter uses a non-ASCII form?
+                                    int cls;
+                                    int64_t e64;
+                                    match_tag(tg, T, x, n, false, cls, e64);
+                                    ex = (int)e64;
+                                }
+                                took = on_tag(x, tend, kind == 1, ex);
                             }
-                            on_tag(x, tend, kind == 1, ex);
+                            if (!took && depth == 0) hold_candidate(T, x);
                         };
                         if (c <= kRecInline) {
 #pragma unroll
@@ -752,7 +799,7 @@ struct StreamRunWalker {
             const int nclosed = nruns;       // runs ended by an open tag
             if (depth == 0) close_run(n);    // the final run, clipped later at the last release boundary
             has_final = nruns > nclosed;
-            if (nruns > kDescRuns) {
+            if (nruns > kDescRuns || nh > kDescHolds) {
                 overflow = true;
                 return res;
             }
@@ -760,101 +807,22 @@ struct StreamRunWalker {
 
         // ---- 2: feed boundaries, one per lane ----
         int R_last = 0, P_last = 0;
-        bool have_last = false;
-        if (COPY && lane == 0) out_chunk_off[chunk0] = out_base;
-        // every lane gets its own copy of the (at most kDescRuns) run starts: run_of(x) = number of runs that start
-        // at or before x, found with kDescRuns compares; the run's data then comes from the owning lane (shuffle)
-        int rsv[kDescRuns];
-#pragma unroll
-        for (int i = 0; i < kDescRuns; i++) {
-            rsv[i] = __shfl_sync(kFull, run_s, i);
-            if (i >= nruns) rsv[i] = INT32_MAX;
-        }
-        int run_before = 0;  // lane i: kept bytes in runs 0..i-1 (exclusive prefix of run lengths)
-        {
-            const int len = lane < nruns ? run_e - run_s : 0;
-            int incl = len;
-#pragma unroll
-            for (int d = 1; d < kDescRuns; d <<= 1) {
-                int t = __shfl_up_sync(kFull, incl, d);
-                if (lane >= d) incl += t;
+        if (MODE == 2) {  // both are in the descriptor
+            R_last = desc->rlast;
+            P_last = desc->total;
+        } else if (MODE == 0) {  // only the last boundary (c = n) matters here: is it inside a hold interval?
+            const unsigned who = __ballot_sync(kFull, lane < nh && hold_x < n && n <= hold_e);
+            R_last = n;
+            P_last = cum;
+            if (who) {
+                R_last = __shfl_sync(kFull, hold_x, __ffs(who) - 1);
+                P_last = cum - (n - R_last);
             }
-            run_before = incl - len;
-        }
-        const int64_t kb0 = COPY ? 1 : m;
-        int64_t cnext = kb0 + lane <= m ? co[kb0 + lane] : 0;  // boundaries are fetched one batch ahead
-        for (int64_t kb = kb0; kb <= m; kb += 32) {
-            const int64_t k = kb + lane;
-            const bool in = k <= m;
-            const int c = in ? (int)(cnext - ustart) : 0;
-            if (k + 32 <= m) cnext = co[k + 32];
-            // last '<' in [c - kHeldMax, c): look through the records of the step that holds byte c-1 and, when the
-            // window reaches back into it, of the step before (per lane, no warp-wide operation in here)
-            int p = -1;
-            if (in && c > 0) {
-                const int64_t sj = (ustart + c - 1) >> 10;
-#pragma unroll
-                for (int back = 0; back < 2; back++) {
-                    const int64_t sx = sj - back;
-                    if (back == 1 && (p >= 0 || sx < (ustart >> 10) || ((sj << 10) - ustart) <= c - kHeldMax)) break;
-                    const int cnt = ts.cnt[sx];
-                    if (cnt == 0) continue;
-                    const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sx * kRecPerStep);
-                    const uint4 qa = rp[0];
-                    uint4 qb = make_uint4(0, 0, 0, 0);
-                    if (cnt > 4) qb = rp[1];
-                    const int sb = (int)((sx << 10) - ustart);
-                    for (int q = 0; q < cnt; q++) {
-                        const uint32_t rq = q < kRecInline ? rec_select(qa, qb, q) : ts.rec[sx * kRecPerStep + q];
-                        const int x = sb + (int)(rq & 1023);
-                        if (x >= 0 && x < c && x > p) p = x;
-                    }
-                }
-            }
-            // released-candidate bytes before c: carried literal bytes + overlap of [0, c) with the runs; and is the
-            // '<' at p kept text (inside a run)?  One uniform loop over the runs for both.
-            int kc = 0, kp = 0;  // runs starting at or before c-1 / at or before p
-#pragma unroll
-            for (int i = 0; i < kDescRuns; i++) {
-                kc += rsv[i] < c;
-                kp += rsv[i] <= p;
-            }
-            // the last of those runs decides: everything before it is kept in full, it contributes min(c, end) - start
-            const int ic = kc > 0 ? kc - 1 : 0, ip = kp > 0 ? kp - 1 : 0;
-            const int s_c = __shfl_sync(kFull, run_s, ic), e_c = __shfl_sync(kFull, run_e, ic), b_c = __shfl_sync(kFull, run_before, ic);
-            const int e_p = __shfl_sync(kFull, run_e, ip);
-            int P = held_kept;
-            if (kc > 0) P += b_c + (min(c, e_c) - s_c);
-            const bool p_kept = kp > 0 && p < e_p;
-            int R = c;
-            const bool found_lt = p >= 0;
-            if (found_lt && p_kept && c - p <= kHeldMax && tg.hold_enabled && is_tag_prefix(tg, T, p, c, true, false)) {
-                R = p;
-                P -= (c - p);
-            }
-            if (in && !found_lt && held_kept && tg.hold_enabled && c + h <= kHeldMax && is_tag_prefix(tg, A, -h, c, true, false)) {
-                R = -h;
-                P = 0;
-            }
-            if (in) {
-                if (COPY) out_chunk_off[chunk0 + k] = out_base + P;
-                if (k == m) {
-                    R_last = R;
-                    P_last = P;
-                    have_last = true;
-                }
-            }
-        }
-        {
-            const unsigned who = __ballot_sync(kFull, have_last);
-            const int srcl = who ? __ffs(who) - 1 : 0;
-            R_last = __shfl_sync(kFull, R_last, srcl);
-            P_last = __shfl_sync(kFull, P_last, srcl);
         }
         res.total_out = P_last;
         if (MODE == 0) {
             if (desc) {
-                UnitDesc& d = *desc;
+                StreamDesc& d = *desc;
                 if (lane == 0) {
                     d.nruns = nruns;
                     d.total = P_last;
@@ -863,11 +831,17 @@ struct StreamRunWalker {
                     d.last_tok_end = last_tok_end;
                     d.rlast = R_last;
                     d.flags = (held_unconsumed ? 1 : 0) | (has_final ? 2 : 0) | (held_kept ? 4 : 0);
+                    d.held_len = h;
+                    d.ustart = ustart;
                     d.pad = 0;
                 }
                 if (lane < kDescRuns) {  // unclipped; the copy clips the open-ended final run at rlast
                     d.run_s[lane] = lane < nruns ? run_s : 0;
                     d.run_e[lane] = lane < nruns ? run_e : 0;
+                }
+                if (lane < kDescHolds) {
+                    d.hold_x[lane] = lane < nh ? hold_x : INT32_MAX;
+                    d.hold_e[lane] = lane < nh ? hold_e : INT32_MIN;
                 }
             }
             return res;
@@ -1191,7 +1165,7 @@ struct StripRunWalker {
                     d.last_tok_end = -1;
                     d.rlast = n;
                     d.flags = 0;
-                    d.pad = 0;
+                    d.held_len = 0;
                 }
                 if (lane < kDescRuns) {
                     d.run_s[lane] = lane < nruns ? run_s : 0;

@@ -302,6 +302,8 @@ __global__ void request_finalize_kernel(const int64_t* __restrict__ req_off, int
 }
 
 // Warp-cooperative copy of a unit's kept runs (descriptor) to dst: run i goes to dst + held_kept + (lengths before it).
+// PHASE 0: prefetch the source lines and copy; 1: prefetch only; 2: copy only (the caller put work between the two).
+template <int PHASE>
 __device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, const uint8_t* src, uint8_t* dst,
                                             const uint8_t* src_hi, int lane) {
     const int nruns = dp->nruns;
@@ -320,16 +322,20 @@ __device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, con
         if (lane >= d) incl += t;
     }
     const int off = dp->held_kept + incl - len;
-    if (__shfl_sync(kFull, incl, kDescRuns - 1) <= 64 * nruns) {  // short runs: one run per lane, byte by byte
+    const bool tiny = __shfl_sync(kFull, incl, kDescRuns - 1) <= 64 * nruns;  // short runs: one run per lane, byte by byte
+    if (PHASE != 2 && !tiny) {
+        for (int i = 0; i < nruns; i++) {  // get every source line of every run moving before the first copy waits on one
+            const int s_i = __shfl_sync(kFull, rs, i), l_i = __shfl_sync(kFull, len, i);
+            const uint8_t* a = src + s_i;
+            const uint8_t* base = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(a) & ~(uintptr_t)127);
+            const int64_t bytes = (a - base) + l_i;
+            for (int64_t o = (int64_t)lane * 128; o < bytes; o += 32 * 128) asm volatile("prefetch.L2 [%0];" ::"l"(base + o));
+        }
+    }
+    if (PHASE == 1) return;
+    if (tiny) {
         for (int k = 0; k < len; k++) dst[off + k] = src[rs + k];
         return;
-    }
-    for (int i = 0; i < nruns; i++) {  // get every source line of every run moving before the first copy waits on one
-        const int s_i = __shfl_sync(kFull, rs, i), l_i = __shfl_sync(kFull, len, i);
-        const uint8_t* a = src + s_i;
-        const uint8_t* base = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(a) & ~(uintptr_t)127);
-        const int64_t bytes = (a - base) + l_i;
-        for (int64_t o = (int64_t)lane * 128; o < bytes; o += 32 * 128) asm volatile("prefetch.L2 [%0];" ::"l"(base + o));
     }
     for (int i = 0; i < nruns; i++) {
         const int s_i = __shfl_sync(kFull, rs, i), l_i = __shfl_sync(kFull, len, i), o_i = __shfl_sync(kFull, off, i);
@@ -364,7 +370,7 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
         } else if (kl > 0) {
             const int nr = desc ? desc[r].nruns : -1;
             if (nr >= 0) {
-                gather_unit(desc + r, in + a, out + d, in + total, lane);
+                gather_unit<0>(desc + r, in + a, out + d, in + total, lane);
             } else if (nr == -2) {  // 9..32 kept runs: walk the records again and copy from the lanes
                 strip_copy_wide(tg, in, total, a, b - a, lastclose[wib], lane, ts, kl, out + d);
             } else {
@@ -382,11 +388,14 @@ __global__ void __launch_bounds__(kThreads, 4)
 stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                     const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                     int64_t n_streams, const StreamState* __restrict__ st_in, uint32_t flags,
-                    int64_t* __restrict__ totals, TokSrc ts, UnitDesc* __restrict__ desc) {
+                    int64_t* __restrict__ totals, TokSrc ts, StreamDesc* __restrict__ desc, int32_t* __restrict__ sid) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
+    const int64_t cb = stream_off[0];
     for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
         const int64_t c0 = stream_off[s], c1 = stream_off[s + 1];
+        if (sid)  // chunk -> stream map of this call, for the thread-per-boundary offsets kernel
+            for (int64_t k = c0 + lane; k < c1; k += 32) sid[k - cb] = (int32_t)s;
         StreamResult r;
         bool slow = ts.cnt == nullptr;
         if (!slow) {
@@ -405,12 +414,12 @@ stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restric
     }
 }
 
+// Byte-rescanning copy pass (QB200_PATH=general and the allocation-free entry point): warp per stream.
 __global__ void __launch_bounds__(kThreads, 4)
 stream_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                    const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                    int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
-                   const int64_t* __restrict__ bases, uint8_t* __restrict__ out, int64_t* __restrict__ out_chunk_off,
-                   TokSrc ts, UnitDesc* __restrict__ desc) {
+                   const int64_t* __restrict__ bases, uint8_t* __restrict__ out, int64_t* __restrict__ out_chunk_off) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
     for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
@@ -418,35 +427,107 @@ stream_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
         // state_in may alias state_out: the walker reads its input state before writing the output state
         StreamState si;
         if (st_in) si = st_in[s];
-        const bool slow = ts.cnt == nullptr || desc[s].nruns < 0;
-        if (!slow) {  // per-chunk offsets, carried literal bytes, carried state; the kept runs go through the gather kernel
-            StreamRunWalker<1> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
-            w.desc = desc + s;
-            w.out_base = bases[s];
-            w.dst = out + bases[s];
-            w.out_chunk_off = out_chunk_off;
-            w.chunk0 = c0;
-            w.run(st_in ? &si : nullptr, st_out ? st_out + s : nullptr);
-        }
-        if (slow)
-            stream_copy_slow(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, st_in ? &si : nullptr,
-                             st_out ? st_out + s : nullptr, bases[s], out, out_chunk_off, c0);
+        stream_copy_slow(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, st_in ? &si : nullptr,
+                         st_out ? st_out + s : nullptr, bases[s], out, out_chunk_off, c0);
         __syncwarp();
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0 && n_streams == 0) out_chunk_off[0] = 0;
 }
 
-// kept runs of every stream -> their final place (descriptor-driven; units redone by the slow walker are skipped)
-__global__ void __launch_bounds__(kThreads, 5)
-stream_gather_kernel(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ chunk_off, int64_t n_chunks,
-                     const int64_t* __restrict__ stream_off, int64_t n_streams, const int64_t* __restrict__ bases,
-                     const UnitDesc* __restrict__ desc, uint8_t* __restrict__ out) {
+// Per-chunk output offsets, a data-parallel map over the feed boundaries: out_chunk_off[k] = bases[s] + (bytes stream s
+// has released by the end of chunk k-1).  Everything sequential was settled by the count kernel (descriptor: kept runs,
+// hold intervals, carried bytes); what is left per boundary is a clamp-sum over at most kDescRuns runs and kDescHolds
+// interval tests.  A thread takes four consecutive boundaries (their loads are issued together; they nearly always share
+// one descriptor), threads are independent: no per-stream chain of dependent loads.
+__global__ void __launch_bounds__(256)
+stream_offsets_kernel(const int64_t* __restrict__ chunk_off, const int64_t* __restrict__ stream_off, int64_t n_streams,
+                      const int64_t* __restrict__ bases, int64_t* __restrict__ out_chunk_off, const StreamDesc* __restrict__ desc,
+                      const int32_t* __restrict__ sid) {
+    const int64_t cb = stream_off[0], nb = stream_off[n_streams] - cb;  // boundary cb + 1 + i ends chunk cb + i, i < nb
+    if (blockIdx.x == 0 && threadIdx.x == 0) out_chunk_off[cb] = bases[0];
+    const int64_t* co = chunk_off + cb + 1;
+    int64_t* oo = out_chunk_off + cb + 1;
+    for (int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i0 < nb; i0 += (int64_t)gridDim.x * blockDim.x * 4) {
+        int sv[4];
+        int64_t pos[4];
+        if (i0 + 4 <= nb) {
+            const int4 v = *reinterpret_cast<const int4*>(sid + i0);
+            sv[0] = v.x, sv[1] = v.y, sv[2] = v.z, sv[3] = v.w;
+#pragma unroll
+            for (int j = 0; j < 4; j++) pos[j] = co[i0 + j];
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                sv[j] = i0 + j < nb ? sid[i0 + j] : -1;
+                pos[j] = i0 + j < nb ? co[i0 + j] : 0;
+            }
+        }
+        int prev = -1, nruns = 0, held_kept = 0;
+        int64_t ustart = 0, base = 0;
+        int4 s0, s1, l0, l1, hx, he;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (sv[j] < 0) continue;
+            if (sv[j] != prev) {
+                prev = sv[j];
+                const StreamDesc* d = desc + prev;
+                nruns = d->nruns;
+                const int4 hd = *reinterpret_cast<const int4*>(&d->last_tok_end);  // last_tok_end, rlast, flags, held_len
+                held_kept = (hd.z & 4) ? hd.w : 0;
+                ustart = d->ustart;
+                base = bases[prev];
+                s0 = *reinterpret_cast<const int4*>(d->run_s), s1 = *reinterpret_cast<const int4*>(d->run_s + 4);
+                l0 = *reinterpret_cast<const int4*>(d->run_e), l1 = *reinterpret_cast<const int4*>(d->run_e + 4);
+                l0.x -= s0.x, l0.y -= s0.y, l0.z -= s0.z, l0.w -= s0.w, l1.x -= s1.x, l1.y -= s1.y, l1.z -= s1.z, l1.w -= s1.w;
+                hx = *reinterpret_cast<const int4*>(d->hold_x), he = *reinterpret_cast<const int4*>(d->hold_e);
+            }
+            if (nruns < 0) continue;  // redone by the byte-rescanning walker, which writes its own offsets
+            const int c = (int)(pos[j] - ustart);
+            int P = held_kept;  // unused run slots are [0, 0): they add nothing
+            P += min(max(c - s0.x, 0), l0.x) + min(max(c - s0.y, 0), l0.y) + min(max(c - s0.z, 0), l0.z) + min(max(c - s0.w, 0), l0.w);
+            if (nruns > 4)
+                P += min(max(c - s1.x, 0), l1.x) + min(max(c - s1.y, 0), l1.y) + min(max(c - s1.z, 0), l1.z) + min(max(c - s1.w, 0), l1.w);
+            // a boundary inside a hold interval releases only the bytes before the held '<' (everything in between is text)
+            if (hx.x != INT32_MAX) {
+                if (c > hx.x && c <= he.x) P -= c - hx.x;
+                if (c > hx.y && c <= he.y) P -= c - hx.y;
+                if (c > hx.z && c <= he.z) P -= c - hx.z;
+                if (c > hx.w && c <= he.w) P -= c - hx.w;
+            }
+            oo[i0 + j] = base + P;
+        }
+    }
+}
+
+// Last kernel of a stream feed: per stream, the kept runs go to their final place (their source lines are prefetched
+// first), the carried literal bytes are written and the carried state is produced.  Units that did not fit the
+// descriptor are redone here by the byte-rescanning walker.
+__global__ void __launch_bounds__(kThreads, 4)
+stream_finish_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
+                     const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
+                     int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
+                     const int64_t* __restrict__ bases, uint8_t* __restrict__ out, int64_t* __restrict__ out_chunk_off,
+                     TokSrc ts, StreamDesc* __restrict__ desc) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
     for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
-        if (desc[s].nruns <= 0) continue;
-        const int64_t a = chunk_off[stream_off[s]];
-        gather_unit(desc + s, bytes + a, out + bases[s], bytes + total, lane);
+        const int64_t c0 = stream_off[s], c1 = stream_off[s + 1];
+        const int64_t base = bases[s];
+        // state_in may alias state_out: the input state is read before the output state is written
+        StreamState si;
+        if (st_in) si = st_in[s];
+        if (c1 > c0 && desc[s].nruns < 0) {
+            stream_copy_slow(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, st_in ? &si : nullptr,
+                             st_out ? st_out + s : nullptr, base, out, out_chunk_off, c0);
+        } else {
+            const uint8_t* src = bytes + chunk_off[c0];
+            if (c1 > c0) gather_unit<1>(desc + s, src, out + base, bytes + total, lane);
+            StreamRunWalker<2> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
+            w.desc = desc + s;
+            w.dst = out + base;
+            w.run(st_in ? &si : nullptr, st_out ? st_out + s : nullptr);
+            if (c1 > c0) gather_unit<2>(desc + s, src, out + base, bytes + total, lane);
+        }
+        __syncwarp();
     }
 }
 
@@ -587,6 +668,7 @@ static size_t strip_general_scratch_bytes(int64_t n_resp, int64_t n_req) {
 }
 
 static size_t desc_scratch_bytes(int64_t n_units) { return align256((size_t)(n_units < 0 ? 0 : n_units) * sizeof(UnitDesc) + 96); }
+static size_t stream_desc_scratch_bytes(int64_t n_units) { return align256((size_t)(n_units < 0 ? 0 : n_units) * sizeof(StreamDesc) + 96); }
 
 size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req, int64_t out_capacity) {
     return strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp) + tok_scratch_bytes(out_capacity) + 256;
@@ -669,10 +751,11 @@ static int64_t tiles_for(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte
 // per tile: look-back state word + TileRec; plus the ticket
 static size_t tile_scratch_bytes(int64_t max_tiles) { return align256((size_t)(max_tiles + 1) * (8 + sizeof(TileRec)) + 64); }
 
+static size_t sid_scratch_bytes(int64_t n_chunks) { return align256((size_t)((n_chunks < 0 ? 0 : n_chunks) + 32) * 4); }
+
 size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity) {
-    (void)n_chunks;
     return stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity)) +
-           desc_scratch_bytes(n_streams) + tok_scratch_bytes(out_capacity) + 256;
+           stream_desc_scratch_bytes(n_streams) + tok_scratch_bytes(out_capacity) + sid_scratch_bytes(n_chunks) + 256;
 }
 
 static int stream_feed_check(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
@@ -714,25 +797,34 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     const StreamState* si = reinterpret_cast<const StreamState*>(state_in);
     StreamState* so = reinterpret_cast<StreamState*>(state_out);
     TokSrc ts;
-    UnitDesc* desc = nullptr;
-    if (use_tokens) {  // descriptors + records live behind the general + tile scratch regions
+    StreamDesc* desc = nullptr;
+    size_t sid_offset = 0;
+    if (use_tokens) {  // descriptors + records (+ the chunk -> stream map) live behind the general + tile scratch regions
         uint8_t* tsp = (uint8_t*)scratch + stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity));
-        desc = (UnitDesc*)tsp;
+        desc = (StreamDesc*)tsp;
         ts = launch_tokenizer(tags->dev, chunk_bytes, chunk_off, stream_off, n_streams, out_capacity,
-                              tsp + desc_scratch_bytes(n_streams), stream);
+                              tsp + stream_desc_scratch_bytes(n_streams), stream);
+        sid_offset = (size_t)(tsp - (uint8_t*)scratch) + stream_desc_scratch_bytes(n_streams) + tok_scratch_bytes(out_capacity);
     }
+    int32_t* sid = use_tokens ? (int32_t*)((uint8_t*)scratch + sid_offset) : nullptr;
     stream_count_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
-                                                                     n_streams, si, flags, totals, ts, desc);
+                                                                     n_streams, si, flags, totals, ts, desc, sid);
     LAUNCHED();
     // chained call: this call's output starts where out_chunk_off[first chunk of the call] says (written by the call before)
     launch_scan(totals, n_streams, bases, (int64_t*)((uint8_t*)bases + align256((size_t)(n_streams + 2) * 8)), stream,
                 chain ? out_chunk_off : nullptr, chain ? stream_off : nullptr);
-    stream_copy_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
-                                                                    n_streams, si, so, flags, bases, out_bytes, out_chunk_off, ts, desc);
-    LAUNCHED();
     if (use_tokens) {
-        stream_gather_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(chunk_bytes, chunk_off, n_chunks, stream_off, n_streams,
-                                                                          bases, desc, out_bytes);
+        int64_t nb = (n_chunks + 1023) / 1024;
+        if (nb > 148 * 64) nb = 148 * 64;
+        if (nb < 1) nb = 1;
+        stream_offsets_kernel<<<(unsigned)nb, 256, 0, stream>>>(chunk_off, stream_off, n_streams, bases, out_chunk_off, desc, sid);
+        LAUNCHED();
+        stream_finish_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(
+            tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, si, so, flags, bases, out_bytes, out_chunk_off, ts, desc);
+        LAUNCHED();
+    } else {
+        stream_copy_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
+                                                                        n_streams, si, so, flags, bases, out_bytes, out_chunk_off);
         LAUNCHED();
     }
     CUDA_TRY(cudaGetLastError());

@@ -48,12 +48,12 @@ static_assert(sizeof(UnitDesc) == 96, "descriptor layout");
 // What a stream adds for the per-chunk offsets (stream_offsets_kernel reads only descriptors, never text or records)
 struct StreamDesc : UnitDesc {
     int64_t ustart;  // flat position of the stream's first byte in this call
-    int64_t pad;
+    uint8_t held[24];  // the carried bytes when they are released as text (held_kept > 0): the finish kernel writes them
     // '<' that stay text at depth 0 and can be held back by a feed boundary: a boundary c with hold_x < c <= hold_e
     // releases only the bytes before hold_x (unused slots never match)
     int32_t hold_x[kDescHolds], hold_e[kDescHolds];
 };
-static_assert(sizeof(StreamDesc) == 144, "descriptor layout");
+static_assert(sizeof(StreamDesc) == 160, "descriptor layout");
 
 // true when any step touched by the unit [ustart, ustart+n) overflowed its record slots (then the unit is walked
 // the slow way, straight from its bytes)
@@ -584,9 +584,7 @@ __device__ __noinline__ int hold_interval_end(const DevTags& tg, const A acc, in
     return lo;
 }
 
-// MODE 0: walk + released total + descriptor (count kernel);  2: carried literal bytes + carried state from the
-// descriptor (finish kernel; the per-chunk offsets come from stream_offsets_kernel)
-template <int MODE>
+// One pass per stream (count kernel): walk, released total, descriptor for the offsets / finish kernels, carried state.
 struct StreamRunWalker {
     StreamDesc* desc = nullptr;
     const DevTags& tg;
@@ -598,7 +596,6 @@ struct StreamRunWalker {
     uint32_t flags;
     TokSrc ts;
     bool overflow = false;
-    uint8_t* dst = nullptr;
 
     __device__ StreamRunWalker(const DevTags& tg_, const uint8_t* buf_, int64_t total_, const int64_t* co_, int64_t m_, int lane_,
                                uint32_t flags_, TokSrc ts_)
@@ -616,7 +613,7 @@ struct StreamRunWalker {
         }
         StreamResult res{0};
         if (m <= 0) {  // nothing fed: state passes through
-            if (MODE != 0 && st_out && lane == 0) {
+            if (st_out && lane == 0) {
                 if (flags & 4u) si.held_len = 0;
                 for (int i = si.held_len; i < kHeldMax; i++) si.held[i] = 0;
                 si.tail_len = -1;
@@ -701,19 +698,7 @@ struct StreamRunWalker {
         };
 
         bool has_final = false;
-        if (MODE != 0) {  // everything phase 1 would find out is in the descriptor
-            const StreamDesc& d = *desc;
-            nruns = d.nruns;
-            held_kept = (d.flags & 4) ? h : 0;
-            depth = d.depth;
-            last_tok_end = d.last_tok_end;
-            held_unconsumed = (d.flags & 1) != 0;
-            has_final = (d.flags & 2) != 0;
-            if (lane < kDescRuns) {
-                run_s = d.run_s[lane];
-                run_e = d.run_e[lane];
-            }
-        } else {
+        {
             // ---- the carried partial tag (positions -h .. -1) ----
             if (h > 0) {
                 int cls;
@@ -807,10 +792,7 @@ struct StreamRunWalker {
 
         // ---- 2: feed boundaries, one per lane ----
         int R_last = 0, P_last = 0;
-        if (MODE == 2) {  // both are in the descriptor
-            R_last = desc->rlast;
-            P_last = desc->total;
-        } else if (MODE == 0) {  // only the last boundary (c = n) matters here: is it inside a hold interval?
+        {  // only the last boundary (c = n) matters here: is it inside a hold interval?
             const unsigned who = __ballot_sync(kFull, lane < nh && hold_x < n && n <= hold_e);
             R_last = n;
             P_last = cum;
@@ -820,7 +802,7 @@ struct StreamRunWalker {
             }
         }
         res.total_out = P_last;
-        if (MODE == 0) {
+        {
             if (desc) {
                 StreamDesc& d = *desc;
                 if (lane == 0) {
@@ -833,8 +815,8 @@ struct StreamRunWalker {
                     d.flags = (held_unconsumed ? 1 : 0) | (has_final ? 2 : 0) | (held_kept ? 4 : 0);
                     d.held_len = h;
                     d.ustart = ustart;
-                    d.pad = 0;
                 }
+                if (held_kept && R_last > -h && lane < h) d.held[lane] = heldp[lane];
                 if (lane < kDescRuns) {  // unclipped; the copy clips the open-ended final run at rlast
                     d.run_s[lane] = lane < nruns ? run_s : 0;
                     d.run_e[lane] = lane < nruns ? run_e : 0;
@@ -844,13 +826,9 @@ struct StreamRunWalker {
                     d.hold_e[lane] = lane < nh ? hold_e : INT32_MIN;
                 }
             }
-            return res;
         }
 
-        // ---- 3: carried literal bytes and carried state (the kept runs are copied by the gather kernel) ----
-        if (held_kept && R_last > -h) {
-            if (lane < h) dst[lane] = heldp[lane];
-        }
+        // ---- 3: carried state (the kept runs and the carried literal bytes are written by the finish kernel) ----
         if (st_out) {
             int hp = INT32_MIN;  // start of the carried tail (logical coords)
             if (!(flags & 4u)) {
@@ -869,6 +847,7 @@ struct StreamRunWalker {
                     if (p != INT32_MIN && is_tag_prefix(tg, A, p, n, false, true)) hp = p;
                 }
             }
+            __syncwarp();  // state_in may alias state_out: every lane is done reading the carried bytes
             if (lane == 0) {
                 StreamState so;
                 so.depth = depth;

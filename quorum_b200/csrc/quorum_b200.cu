@@ -387,7 +387,7 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
 __global__ void __launch_bounds__(kThreads, 4)
 stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                     const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
-                    int64_t n_streams, const StreamState* __restrict__ st_in, uint32_t flags,
+                    int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
                     int64_t* __restrict__ totals, TokSrc ts, StreamDesc* __restrict__ desc, int32_t* __restrict__ sid) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
@@ -399,10 +399,12 @@ stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restric
         StreamResult r;
         bool slow = ts.cnt == nullptr;
         if (!slow) {
-            StreamRunWalker<0> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
+            StreamRunWalker w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
             w.desc = desc + s;
-            if (c1 <= c0 && lane == 0) desc[s].nruns = 0;  // nothing fed: state passes through, nothing to copy
-            r = w.run(st_in ? st_in + s : nullptr, nullptr);
+            if (c1 <= c0 && lane == 0) desc[s].nruns = desc[s].held_kept = 0;  // nothing fed: state passes through, nothing to copy
+            // record-driven units get their carried state here (st_in may alias st_out; a unit that overflows returns
+            // before it writes any and is redone, state included, by the finish kernel)
+            r = w.run(st_in ? st_in + s : nullptr, st_out ? st_out + s : nullptr);
             slow = w.overflow;  // does not fit the descriptor: redo this unit from its bytes
         }
         if (slow) {
@@ -498,34 +500,31 @@ stream_offsets_kernel(const int64_t* __restrict__ chunk_off, const int64_t* __re
     }
 }
 
-// Last kernel of a stream feed: per stream, the kept runs go to their final place (their source lines are prefetched
-// first), the carried literal bytes are written and the carried state is produced.  Units that did not fit the
-// descriptor are redone here by the byte-rescanning walker.
-__global__ void __launch_bounds__(kThreads, 4)
+// Last kernel of a stream feed: per stream, the kept runs and the released carried bytes go to their final place; all it
+// reads besides the text is the stream's descriptor.  Units that did not fit the descriptor are redone here, offsets and
+// carried state included, by the byte-rescanning walker.
+__global__ void __launch_bounds__(kThreads, 5)
 stream_finish_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                      const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                      int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
                      const int64_t* __restrict__ bases, uint8_t* __restrict__ out, int64_t* __restrict__ out_chunk_off,
-                     TokSrc ts, StreamDesc* __restrict__ desc) {
+                     const StreamDesc* __restrict__ desc) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
     for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
-        const int64_t c0 = stream_off[s], c1 = stream_off[s + 1];
+        const StreamDesc* d = desc + s;
+        const int nruns = d->nruns;
         const int64_t base = bases[s];
-        // state_in may alias state_out: the input state is read before the output state is written
-        StreamState si;
-        if (st_in) si = st_in[s];
-        if (c1 > c0 && desc[s].nruns < 0) {
+        if (nruns < 0) {
+            const int64_t c0 = stream_off[s], c1 = stream_off[s + 1];
+            StreamState si;  // state_in may alias state_out: the input state is read before the output state is written
+            if (st_in) si = st_in[s];
             stream_copy_slow(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, st_in ? &si : nullptr,
                              st_out ? st_out + s : nullptr, base, out, out_chunk_off, c0);
         } else {
-            const uint8_t* src = bytes + chunk_off[c0];
-            if (c1 > c0) gather_unit<1>(desc + s, src, out + base, bytes + total, lane);
-            StreamRunWalker<2> w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
-            w.desc = desc + s;
-            w.dst = out + base;
-            w.run(st_in ? &si : nullptr, st_out ? st_out + s : nullptr);
-            if (c1 > c0) gather_unit<2>(desc + s, src, out + base, bytes + total, lane);
+            const int hk = d->held_kept;
+            if (lane < hk) out[base + lane] = d->held[lane];
+            if (nruns > 0) gather_unit<0>(d, bytes + d->ustart, out + base, bytes + total, lane);
         }
         __syncwarp();
     }
@@ -808,7 +807,7 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     }
     int32_t* sid = use_tokens ? (int32_t*)((uint8_t*)scratch + sid_offset) : nullptr;
     stream_count_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
-                                                                     n_streams, si, flags, totals, ts, desc, sid);
+                                                                     n_streams, si, use_tokens ? so : nullptr, flags, totals, ts, desc, sid);
     LAUNCHED();
     // chained call: this call's output starts where out_chunk_off[first chunk of the call] says (written by the call before)
     launch_scan(totals, n_streams, bases, (int64_t*)((uint8_t*)bases + align256((size_t)(n_streams + 2) * 8)), stream,
@@ -820,7 +819,7 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
         stream_offsets_kernel<<<(unsigned)nb, 256, 0, stream>>>(chunk_off, stream_off, n_streams, bases, out_chunk_off, desc, sid);
         LAUNCHED();
         stream_finish_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(
-            tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, si, so, flags, bases, out_bytes, out_chunk_off, ts, desc);
+            tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, si, so, flags, bases, out_bytes, out_chunk_off, desc);
         LAUNCHED();
     } else {
         stream_copy_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,

@@ -444,30 +444,27 @@ __global__ void __launch_bounds__(256)
 stream_offsets_kernel(const int64_t* __restrict__ chunk_off, const int64_t* __restrict__ stream_off, int64_t n_streams,
                       const int64_t* __restrict__ bases, int64_t* __restrict__ out_chunk_off, const StreamDesc* __restrict__ desc,
                       const int32_t* __restrict__ sid) {
+    constexpr int PER = 4;  // boundaries per thread; a warp takes 32 * PER consecutive ones, lane-interleaved (coalesced)
     const int64_t cb = stream_off[0], nb = stream_off[n_streams] - cb;  // boundary cb + 1 + i ends chunk cb + i, i < nb
     if (blockIdx.x == 0 && threadIdx.x == 0) out_chunk_off[cb] = bases[0];
     const int64_t* co = chunk_off + cb + 1;
     int64_t* oo = out_chunk_off + cb + 1;
-    for (int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i0 < nb; i0 += (int64_t)gridDim.x * blockDim.x * 4) {
-        int sv[4];
-        int64_t pos[4];
-        if (i0 + 4 <= nb) {
-            const int4 v = *reinterpret_cast<const int4*>(sid + i0);
-            sv[0] = v.x, sv[1] = v.y, sv[2] = v.z, sv[3] = v.w;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t i0 = warp * (32 * PER) + lane; i0 < nb; i0 += nwarps * (32 * PER)) {
+        int sv[PER];
+        int64_t pos[PER];
 #pragma unroll
-            for (int j = 0; j < 4; j++) pos[j] = co[i0 + j];
-        } else {
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                sv[j] = i0 + j < nb ? sid[i0 + j] : -1;
-                pos[j] = i0 + j < nb ? co[i0 + j] : 0;
-            }
+        for (int j = 0; j < PER; j++) {
+            const int64_t i = i0 + 32 * j;
+            sv[j] = i < nb ? sid[i] : -1;
+            pos[j] = i < nb ? co[i] : 0;
         }
         int prev = -1, nruns = 0, held_kept = 0;
         int64_t ustart = 0, base = 0;
         int4 s0, s1, l0, l1, hx, he;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
+        for (int j = 0; j < PER; j++) {
             if (sv[j] < 0) continue;
             if (sv[j] != prev) {
                 prev = sv[j];
@@ -495,7 +492,7 @@ stream_offsets_kernel(const int64_t* __restrict__ chunk_off, const int64_t* __re
                 if (c > hx.z && c <= he.z) P -= c - hx.z;
                 if (c > hx.w && c <= he.w) P -= c - hx.w;
             }
-            oo[i0 + j] = base + P;
+            oo[i0 + 32 * j] = base + P;
         }
     }
 }

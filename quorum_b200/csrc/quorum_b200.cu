@@ -384,7 +384,7 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
 // ---------------------------------------------------------------------------------------------------------------
 // kernels: stream feed
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 6)
 stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                     const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                     int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
@@ -646,7 +646,7 @@ static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const in
     TokSrc ts;
     uint8_t* cnt = scratch;
     uint32_t* rec = (uint32_t*)(scratch + align256((size_t)st));
-    int64_t blocks = (st + 7) / 8;
+    int64_t blocks = (st / 2 + 8) / 8;  // a warp takes two steps per iteration
     const int64_t cap = 148 * 8 * 4;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;

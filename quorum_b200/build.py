@@ -1,13 +1,12 @@
 """Builds quorum_b200/libquorum_b200.so in-tree with nvcc for sm_100a (cross-compiles without a GPU)."""
+import glob
 import os
 import subprocess
 import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "quorum_b200.cu")
-DEPS = [SRC, os.path.join(HERE, "csrc", "qb_common.cuh"), os.path.join(HERE, "csrc", "qb_walk.cuh"),
-        os.path.join(HERE, "csrc", "qb_tile.cuh"),
-        os.path.join(os.path.dirname(HERE), "include", "quorum_b200.h")]
+DEPS = sorted(glob.glob(os.path.join(HERE, "csrc", "*"))) + [os.path.join(os.path.dirname(HERE), "include", "quorum_b200.h")]
 LIB = os.path.join(HERE, "libquorum_b200.so")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

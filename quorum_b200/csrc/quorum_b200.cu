@@ -17,6 +17,7 @@
 #include "qb_walk.cuh"
 #include "qb_tile.cuh"
 #include "qb_tok.cuh"
+#include "qb_lane.cuh"
 #include "qb_sse.cuh"
 #include <stdlib.h>
 
@@ -384,35 +385,74 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
 // ---------------------------------------------------------------------------------------------------------------
 // kernels: stream feed
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 6)
+// First kernel after the tokenizer: every stream is walked (tag automaton over its token records), which gives the bytes
+// it releases (totals -> scan -> bases), its descriptor (kept runs, hold intervals, carried bytes) and its carried state.
+// A warp takes 32 consecutive streams, one per lane (qb_lane.cuh); streams that touch more than lane_steps steps, or do
+// not fit the descriptor, are then walked one at a time by the whole warp.  No tokens (QB200_PATH=general): the
+// byte-rescanning count of every stream.
+__global__ void __launch_bounds__(kThreads, 4)
 stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                     const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                     int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
-                    int64_t* __restrict__ totals, TokSrc ts, StreamDesc* __restrict__ desc, int32_t* __restrict__ sid) {
+                    int64_t* __restrict__ totals, TokSrc ts, StreamDesc* __restrict__ desc, int32_t* __restrict__ sid,
+                    int lane_steps) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
     const int64_t cb = stream_off[0];
-    for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
-        const int64_t c0 = stream_off[s], c1 = stream_off[s + 1];
-        if (sid)  // chunk -> stream map of this call, for the thread-per-boundary offsets kernel
-            for (int64_t k = c0 + lane; k < c1; k += 32) sid[k - cb] = (int32_t)s;
-        StreamResult r;
-        bool slow = ts.cnt == nullptr;
-        if (!slow) {
-            StreamRunWalker w(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, ts);
-            w.desc = desc + s;
-            if (c1 <= c0 && lane == 0) desc[s].nruns = desc[s].held_kept = 0;  // nothing fed: state passes through, nothing to copy
-            // record-driven units get their carried state here (st_in may alias st_out; a unit that overflows returns
-            // before it writes any and is redone, state included, by the finish kernel)
-            r = w.run(st_in ? st_in + s : nullptr, st_out ? st_out + s : nullptr);
-            slow = w.overflow;  // does not fit the descriptor: redo this unit from its bytes
+    const int64_t ngroups = (n_streams + 31) >> 5;
+    for (int64_t g = (int64_t)blockIdx.x * kWarpsPerBlock + wib; g < ngroups; g += (int64_t)gridDim.x * kWarpsPerBlock) {
+        const int64_t s = (g << 5) + lane;
+        const bool have = s < n_streams;
+        int64_t c0 = 0, c1 = 0, tot = 0;
+        bool done = false;
+        if (have) {
+            c0 = stream_off[s];
+            c1 = stream_off[s + 1];
+            if (ts.cnt) {
+                bool small = true;
+                if (c1 > c0) {
+                    const int64_t a = chunk_off[c0], b = chunk_off[c1];
+                    small = b <= a || ((b - 1) >> 10) - (a >> 10) < lane_steps;
+                }
+                if (small)
+                    done = stream_walk_lane(tg, bytes, chunk_off + c0, c1 - c0, flags, ts, st_in ? st_in + s : nullptr,
+                                            st_out ? st_out + s : nullptr, desc + s, tot);
+            }
         }
-        if (slow) {
-            r = stream_count_slow(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, st_in ? st_in + s : nullptr);
-            if (desc && lane == 0) desc[s].nruns = -1;
-        }
-        if (lane == 0) totals[s] = r.total_out;
         __syncwarp();
+        unsigned todo = __ballot_sync(kFull, have && !done);
+        while (todo) {  // one warp per stream
+            const int j = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int64_t sj = (g << 5) + j;
+            const int64_t d0 = __shfl_sync(kFull, c0, j), d1 = __shfl_sync(kFull, c1, j);
+            StreamResult r;
+            bool slow = ts.cnt == nullptr;
+            if (!slow) {
+                StreamRunWalker w(tg, bytes, total, chunk_off + d0, d1 - d0, lane, flags, ts);
+                w.desc = desc + sj;
+                if (d1 <= d0 && lane == 0) desc[sj].nruns = desc[sj].held_kept = 0;  // nothing fed: nothing to copy
+                // record-driven units get their carried state here (st_in may alias st_out; a unit that overflows
+                // returns before it writes any and is redone, state included, by the finish kernel)
+                r = w.run(st_in ? st_in + sj : nullptr, st_out ? st_out + sj : nullptr);
+                slow = w.overflow;  // does not fit the descriptor: redo this unit from its bytes
+            }
+            if (slow) {
+                r = stream_count_slow(tg, bytes, total, chunk_off + d0, d1 - d0, lane, flags, st_in ? st_in + sj : nullptr);
+                if (desc && lane == 0) desc[sj].nruns = -1;
+            }
+            if (lane == j) tot = r.total_out;
+            __syncwarp();
+        }
+        if (have) totals[s] = tot;
+        if (sid) {  // chunk -> stream map of this call, for the offsets kernel: the group's chunks, stream by stream
+            const int cnt = n_streams - (g << 5) < 32 ? (int)(n_streams - (g << 5)) : 32;
+            for (int j = 0; j < cnt; j++) {
+                const int64_t d0 = __shfl_sync(kFull, c0, j), d1 = __shfl_sync(kFull, c1, j);
+                const int32_t sv = (int32_t)((g << 5) + j);
+                for (int64_t k = d0 + lane; k < d1; k += 32) sid[k - cb] = sv;
+            }
+        }
     }
 }
 
@@ -647,7 +687,7 @@ static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const in
     uint8_t* cnt = scratch;
     uint32_t* rec = (uint32_t*)(scratch + align256((size_t)st));
     int64_t blocks = (st / 2 + 8) / 8;  // a warp takes two steps per iteration
-    const int64_t cap = 148 * 8 * 4;
+    const int64_t cap = 148 * 32;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     tokenize_kernel<<<(unsigned)blocks, 256, 0, stream>>>(tg, bytes, off, idx, n, cnt, rec, st);
@@ -803,8 +843,10 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
         sid_offset = (size_t)(tsp - (uint8_t*)scratch) + stream_desc_scratch_bytes(n_streams) + tok_scratch_bytes(out_capacity);
     }
     int32_t* sid = use_tokens ? (int32_t*)((uint8_t*)scratch + sid_offset) : nullptr;
-    stream_count_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
-                                                                     n_streams, si, use_tokens ? so : nullptr, flags, totals, ts, desc, sid);
+    static const int lane_steps = getenv("QB200_LANE_STEPS") ? atoi(getenv("QB200_LANE_STEPS")) : 40;  // 0: warp per stream only
+    stream_count_kernel<<<grid_for((n_streams + 31) / 32), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
+                                                                                 n_streams, si, use_tokens ? so : nullptr, flags, totals,
+                                                                                 ts, desc, sid, lane_steps);
     LAUNCHED();
     // chained call: this call's output starts where out_chunk_off[first chunk of the call] says (written by the call before)
     launch_scan(totals, n_streams, bases, (int64_t*)((uint8_t*)bases + align256((size_t)(n_streams + 2) * 8)), stream,

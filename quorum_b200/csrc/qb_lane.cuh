@@ -236,4 +236,146 @@ __device__ __forceinline__ bool stream_walk_lane(const DevTags& tg, const uint8_
     return true;
 }
 
+// Lane-per-response strip_thinking_tags (same semantics and descriptor as StripRunWalker<false>): liveness of an open tag
+// ("a closer of its class follows", oai_proxy.py:137-139 as restated in SURVEY.md A.1) comes from one backward pass over
+// the response's records that keeps a bit per class; the forward pass is the two-state automaton; `.strip()` looks at
+// the two ends of the run list.  Returns false (nothing written) when the response needs the warp walker: 2 GiB and
+// more, overflowed record slots, more than 64 records, more than kDescRuns kept runs.
+__device__ __forceinline__ bool strip_walk_lane(const DevTags& tg, const uint8_t* buf, int64_t ustart, int64_t n64, const TokSrc& ts,
+                                                UnitDesc* dsc, int64_t& kept_len) {
+    kept_len = 0;
+    if (n64 <= 0) {  // empty response: nothing to walk, nothing to copy
+        dsc->nruns = 0;
+        return true;
+    }
+    if (n64 >= (int64_t)1 << 31) return false;
+    const int n = (int)n64;
+    const PtrAcc T{buf + ustart};
+    const int64_t s_first = ustart >> 10, s_last = (ustart + n - 1) >> 10;
+    int tot = 0;
+    for (int64_t sj = s_first; sj <= s_last; sj++) {
+        const int cnt = ts.cnt[sj];
+        if (cnt == kRecOverflow) return false;
+        tot += cnt;
+    }
+    if (tot > 64) return false;
+    // backward: which open tags are live?  bit i of `live` <-> the i-th record of the response (all kinds counted)
+    unsigned long long live = 0, seen0 = 0, seen1 = 0;  // seen: classes that have a closer further on
+    if (tot > 0) {
+        int idx = tot;
+        for (int64_t sj = s_last; sj >= s_first; sj--) {
+            const int cnt = ts.cnt[sj];
+            const uint32_t* rp = ts.rec + sj * kRecPerStep;
+            const int sb = (int)((sj << 10) - ustart);
+            for (int q = cnt - 1; q >= 0; q--) {
+                idx--;
+                const uint32_t r = rp[q];
+                const int kind = (r >> 17) & 3;
+                const int x = sb + (int)(r & 1023);
+                const int tend = x + (int)((r >> 10) & 127);
+                if (kind == 2 || x < 0 || tend > n) continue;
+                const int cls = (r >> 19) & 127;
+                const unsigned long long bit = 1ull << (cls & 63);
+                if (kind == 1) {
+                    if (cls < 64) seen0 |= bit;
+                    else seen1 |= bit;
+                } else if ((cls < 64 ? seen0 : seen1) & bit) {
+                    live |= 1ull << idx;
+                }
+            }
+        }
+    }
+    // forward: the automaton over the tags in position order
+    int rs[kDescRuns], re[kDescRuns];
+    int nruns = 0, state = -1, seg_start = 0;
+    if (live) {  // no live open tag: the whole response is one run
+        int idx = 0;
+        for (int64_t sj = s_first; sj <= s_last; sj++) {
+            const int cnt = ts.cnt[sj];
+            const uint32_t* rp = ts.rec + sj * kRecPerStep;
+            const int sb = (int)((sj << 10) - ustart);
+            for (int q = 0; q < cnt; q++, idx++) {
+                const uint32_t r = rp[q];
+                const int kind = (r >> 17) & 3;
+                const int x = sb + (int)(r & 1023);
+                const int tend = x + (int)((r >> 10) & 127);
+                if (kind == 2 || x < 0 || tend > n) continue;
+                const int cls = (r >> 19) & 127;
+                if (state < 0) {
+                    if (kind == 0 && ((live >> idx) & 1ull)) {
+                        if (x > seg_start) {
+                            if (nruns < kDescRuns) {
+                                rs[nruns] = seg_start;
+                                re[nruns] = x;
+                            }
+                            nruns++;
+                        }
+                        state = cls;
+                    }
+                } else if (kind == 1 && cls == state) {
+                    seg_start = tend;
+                    state = -1;
+                }
+            }
+        }
+    }
+    if (n > seg_start) {
+        if (nruns < kDescRuns) {
+            rs[nruns] = seg_start;
+            re[nruns] = n;
+        }
+        nruns++;
+    }
+    if (nruns > kDescRuns) return false;
+    // .strip(): white space goes from the front of the first run that keeps anything and from the back of the last
+    int lead = -1;
+    for (int i = 0; i < nruns && lead < 0; i++) {
+        int f = -1;
+        for (int x = rs[i]; x < re[i]; x++)
+            if (!is_white_byte(T, x, n)) {
+                f = x;
+                break;
+            }
+        if (f >= 0) {
+            rs[i] = f;
+            lead = i;
+        } else {
+            re[i] = rs[i];  // all white
+        }
+    }
+    if (lead >= 0) {
+        for (int i = nruns - 1; i >= lead; i--) {
+            int l = -1;
+            for (int x = re[i] - 1; x >= rs[i]; x--)
+                if (!is_white_byte(T, x, n)) {
+                    l = x;
+                    break;
+                }
+            if (l >= 0) {
+                re[i] = l + 1;
+                break;
+            }
+            re[i] = rs[i];
+        }
+    }
+    int kl = 0;
+    for (int i = 0; i < nruns; i++) kl += re[i] - rs[i];
+    kept_len = kl;
+    UnitDesc& d = *dsc;
+    d.nruns = nruns;
+    d.total = kl;
+    d.held_kept = 0;
+    d.depth = 0;
+    d.last_tok_end = -1;
+    d.rlast = n;
+    d.flags = 0;
+    d.held_len = 0;
+#pragma unroll
+    for (int i = 0; i < kDescRuns; i++) {
+        d.run_s[i] = i < nruns ? rs[i] : 0;
+        d.run_e[i] = i < nruns ? re[i] : 0;
+    }
+    return true;
+}
+
 }  // namespace qb

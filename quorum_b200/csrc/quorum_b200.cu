@@ -116,36 +116,59 @@ __device__ __forceinline__ void prefetch_unit_meta(const TokSrc& ts, const uint8
 }
 
 // scratch layout for strip_concat: int64 klen[n_resp] | int64 first[n_resp] | int64 dst[n_resp] | int64 reqlen[n_req+1]
-__global__ void __launch_bounds__(kThreads, 5)
+__global__ void __launch_bounds__(kThreads, 4)
 strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
                    int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first, TokSrc ts,
-                   UnitDesc* __restrict__ desc) {
+                   UnitDesc* __restrict__ desc, int lane_steps) {
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
-    for (int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib; r < n_resp; r += (int64_t)gridDim.x * kWarpsPerBlock) {
-        const int64_t a = in_off[r], b = in_off[r + 1];
-        StripResult res;
-        bool slow = ts.cnt == nullptr;
-        if (!slow) {
-            StripRunWalker<false> w(tg, in, total, a, b - a, lastclose[wib], lane, ts);
-            w.desc = desc + r;
-            if (b == a && lane == 0) desc[r].nruns = 0;  // empty response: nothing to walk, nothing to copy
-            w.run();
-            res.kept_len = w.kept_len;
-            res.first_pos = 0;
-            slow = w.overflow;
-            if (w.many) slow = !strip_count_wide(tg, in, total, a, b - a, lastclose[wib], lane, ts, desc + r, &res.kept_len);
-        }
-        if (slow) {
-            res = strip_count_slow(tg, in, total, a, b - a, lastclose[wib], lane);
-            if (desc && lane == 0) desc[r].nruns = -1;  // redone from the bytes by the copy kernel
-        }
-        if (lane == 0) {
-            klen[r] = res.kept_len;
-            first[r] = res.first_pos;
+    const int64_t ngroups = (n_resp + 31) >> 5;
+    // a warp takes 32 consecutive responses, one per lane (qb_lane.cuh); the ones too long for a lane or that do not fit
+    // a descriptor are then walked one at a time by the whole warp
+    for (int64_t g = (int64_t)blockIdx.x * kWarpsPerBlock + wib; g < ngroups; g += (int64_t)gridDim.x * kWarpsPerBlock) {
+        const int64_t r = (g << 5) + lane;
+        const bool have = r < n_resp;
+        int64_t a = 0, b = 0, kl = 0, fp = 0;
+        bool done = false;
+        if (have) {
+            a = in_off[r];
+            b = in_off[r + 1];
+            if (ts.cnt && (b <= a || ((b - 1) >> 10) - (a >> 10) < lane_steps)) done = strip_walk_lane(tg, in, a, b - a, ts, desc + r, kl);
         }
         __syncwarp();
+        unsigned todo = __ballot_sync(kFull, have && !done);
+        while (todo) {  // one warp per response
+            const int j = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int64_t rj = (g << 5) + j;
+            const int64_t aj = __shfl_sync(kFull, a, j), bj = __shfl_sync(kFull, b, j);
+            StripResult res;
+            bool slow = ts.cnt == nullptr;
+            if (!slow) {
+                StripRunWalker<false> w(tg, in, total, aj, bj - aj, lastclose[wib], lane, ts);
+                w.desc = desc + rj;
+                if (bj == aj && lane == 0) desc[rj].nruns = 0;  // empty response: nothing to walk, nothing to copy
+                w.run();
+                res.kept_len = w.kept_len;
+                res.first_pos = 0;
+                slow = w.overflow;
+                if (w.many) slow = !strip_count_wide(tg, in, total, aj, bj - aj, lastclose[wib], lane, ts, desc + rj, &res.kept_len);
+            }
+            if (slow) {
+                res = strip_count_slow(tg, in, total, aj, bj - aj, lastclose[wib], lane);
+                if (desc && lane == 0) desc[rj].nruns = -1;  // redone from the bytes by the copy kernel
+            }
+            if (lane == j) {
+                kl = res.kept_len;
+                fp = res.first_pos;
+            }
+            __syncwarp();
+        }
+        if (have) {
+            klen[r] = kl;
+            first[r] = fp;
+        }
     }
 }
 
@@ -756,8 +779,9 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
         ts = launch_tokenizer(tags->dev, in_bytes, in_off, nullptr, n_resp, out_capacity,
                               (uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp), stream);
     if (hide && n_resp > 0) {
-        strip_count_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts,
-                                                                     ts.cnt ? desc : nullptr);
+        static const int lane_steps = getenv("QB200_LANE_STEPS") ? atoi(getenv("QB200_LANE_STEPS")) : 40;  // 0: warp per response only
+        strip_count_kernel<<<grid_for((n_resp + 31) / 32), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts,
+                                                                                 ts.cnt ? desc : nullptr, lane_steps);
         LAUNCHED();
     }
     const int tb = 256;

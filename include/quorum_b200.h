@@ -149,6 +149,14 @@ int qb200_sse_frame_batch(const uint8_t *in_bytes, const int64_t *in_off, int64_
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 int64_t qb200_launch_count(void);
 
+/* Per-kernel split of the calls made between the two functions, without a profiler attached: while enabled, the library
+ * records a CUDA event on the launching stream after each of its kernel launches.  qb200_profile_end synchronises on the
+ * last event and returns the number of launches seen (at most max_entries are written): names[i] is a static string
+ * (the kernel), ms[i] the time from the previous event to this one.  Measurement aid for bench.py; process-wide, not
+ * thread-safe, no counterpart in the reference. */
+int qb200_profile_begin(void *stream);
+int32_t qb200_profile_end(const char **names, float *ms, int32_t max_entries);
+
 #ifdef __cplusplus
 }
 #endif

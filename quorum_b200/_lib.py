@@ -16,7 +16,7 @@ EXPORTS = [
     "qb200_last_error", "qb200_tags_create", "qb200_tags_destroy", "qb200_strip_concat_scratch_bytes",
     "qb200_strip_concat_batch", "qb200_stream_feed_scratch_bytes", "qb200_stream_feed_batch",
     "qb200_stream_flush_batch", "qb200_launch_count", "qb200_stream_feed_batch_noalloc",
-    "qb200_sse_frame_scratch_bytes", "qb200_sse_frame_batch",
+    "qb200_sse_frame_scratch_bytes", "qb200_sse_frame_batch", "qb200_profile_begin", "qb200_profile_end",
 ]
 NOALLOC_MAX_STREAMS = 65536
 
@@ -57,6 +57,10 @@ def lib() -> ctypes.CDLL:
     L.qb200_sse_frame_scratch_bytes.argtypes = [i64]
     L.qb200_sse_frame_batch.restype = ctypes.c_int
     L.qb200_sse_frame_batch.argtypes = [vp, vp, i64, vp, vp, vp, i32, vp, i32, u32, vp, i64, vp, vp, sz, vp]
+    L.qb200_profile_begin.restype = ctypes.c_int
+    L.qb200_profile_begin.argtypes = [vp]
+    L.qb200_profile_end.restype = i32
+    L.qb200_profile_end.argtypes = [ctypes.POINTER(ctypes.c_char_p), ctypes.POINTER(ctypes.c_float), i32]
     L.qb200_stream_flush_batch.restype = ctypes.c_int
     L.qb200_stream_flush_batch.argtypes = [vp, i64, vp]
     L.qb200_launch_count.restype = i64
@@ -75,3 +79,18 @@ def check(rc: int) -> None:
 
 def launch_count() -> int:
     return int(lib().qb200_launch_count())
+
+
+def profile_begin(stream_ptr: int = 0) -> None:
+    """Start recording one CUDA event per kernel launch of this library (see include/quorum_b200.h)."""
+    check(lib().qb200_profile_begin(ctypes.c_void_p(stream_ptr)))
+
+
+def profile_end(max_entries: int = 4096):
+    """[(kernel name, milliseconds)] for the launches since profile_begin, in launch order."""
+    names = (ctypes.c_char_p * max_entries)()
+    ms = (ctypes.c_float * max_entries)()
+    n = lib().qb200_profile_end(names, ms, max_entries)
+    if n < 0:
+        check(n)
+    return [(names[i].decode(), float(ms[i])) for i in range(n)]

@@ -11,6 +11,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <vector>
 #include <new>
 
 #include "../../include/quorum_b200.h"
@@ -41,7 +42,18 @@ static int fail(int code, const char* fmt, const char* a = "") {
         if (e_ != cudaSuccess) return fail(QB200_ECUDA, "CUDA error: %s", cudaGetErrorString(e_)); \
     } while (0)
 
-#define LAUNCHED() (g_launches.fetch_add(1, std::memory_order_relaxed))
+// Every kernel launch goes through here: the launch counter, and (qb200_profile_begin) a CUDA event after the launch on
+// the launching stream so that a benchmark can read the per-kernel split of a call without a profiler attached.
+struct ProfMark { const char* name; cudaEvent_t ev; };
+static bool g_prof_on = false;
+static std::vector<ProfMark> g_prof;
+static void prof_mark(const char* name, cudaStream_t stream) {
+    ProfMark m{name, nullptr};
+    if (cudaEventCreate(&m.ev) != cudaSuccess) return;
+    cudaEventRecord(m.ev, stream);
+    g_prof.push_back(m);
+}
+#define LAUNCHED(name) do { g_launches.fetch_add(1, std::memory_order_relaxed); if (g_prof_on) prof_mark(name, stream); } while (0)
 
 // ---------------------------------------------------------------------------------------------------------------
 // Byte-rescanning walkers, out of line: used when no tokenizer records exist (QB200_PATH=general, the no-alloc entry
@@ -302,16 +314,16 @@ static void launch_scan(const int64_t* v, int64_t n, int64_t* out, int64_t* part
                         const int64_t* init_arr = nullptr, const int64_t* init_idx = nullptr) {
     if (n <= 4 * kScanSlice) {
         scan_kernel<<<1, 1024, 0, stream>>>(v, n, out, init_arr, init_idx);
-        LAUNCHED();
+        LAUNCHED("scan_kernel");
         return;
     }
     const int64_t nb = (n + kScanSlice - 1) / kScanSlice;
     scan_partials_kernel<<<(unsigned)nb, 256, 0, stream>>>(v, n, partial);
-    LAUNCHED();
+    LAUNCHED("scan_partials_kernel");
     scan_kernel<<<1, 1024, 0, stream>>>(partial, nb, partial, nullptr, nullptr);
-    LAUNCHED();
+    LAUNCHED("scan_kernel");
     scan_apply_kernel<<<(unsigned)nb, 256, 0, stream>>>(v, n, partial, nb, out, init_arr, init_idx);
-    LAUNCHED();
+    LAUNCHED("scan_apply_kernel");
 }
 
 // dst[r] += out_off[request of r]   (thread per request)
@@ -606,6 +618,32 @@ const char* qb200_last_error(void) { return g_err; }
 
 int64_t qb200_launch_count(void) { return g_launches.load(); }
 
+int qb200_profile_begin(void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    for (auto& m : g_prof) cudaEventDestroy(m.ev);
+    g_prof.clear();
+    g_prof_on = true;
+    prof_mark("(begin)", stream);
+    return QB200_OK;
+}
+
+int32_t qb200_profile_end(const char** names, float* ms, int32_t max_entries) {
+    g_prof_on = false;
+    int32_t n = 0;
+    if (!g_prof.empty()) CUDA_TRY(cudaEventSynchronize(g_prof.back().ev));
+    for (size_t i = 1; i < g_prof.size(); i++) {
+        if (n >= max_entries) break;
+        float t = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&t, g_prof[i - 1].ev, g_prof[i].ev));
+        names[n] = g_prof[i].name;
+        ms[n] = t;
+        n++;
+    }
+    for (auto& m : g_prof) cudaEventDestroy(m.ev);
+    g_prof.clear();
+    return n;
+}
+
 int qb200_tags_create(const uint8_t* names, const int32_t* name_off, int32_t n_tags, qb200_tags** out) {
     if (!out || n_tags < 0 || (n_tags > 0 && (!names || !name_off))) return fail(QB200_EINVAL, "tags_create: bad argument");
     qb200_tags* t = new (std::nothrow) qb200_tags();
@@ -714,7 +752,7 @@ static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const in
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     tokenize_kernel<<<(unsigned)blocks, 256, 0, stream>>>(tg, bytes, off, idx, n, cnt, rec, st);
-    LAUNCHED();
+    LAUNCHED("tokenize_kernel");
     ts.cnt = cnt;
     ts.rec = rec;
     return ts;
@@ -758,7 +796,7 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     CUDA_TRY(cudaGetDeviceCount(&dev_count));
     if (n_req == 0) {
         set_i64_kernel<<<1, 1, 0, stream>>>(out_off, 0);
-        LAUNCHED();
+        LAUNCHED("set_i64_kernel");
         CUDA_TRY(cudaGetLastError());
         return QB200_OK;
     }
@@ -782,20 +820,20 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
         static const int lane_steps = getenv("QB200_LANE_STEPS") ? atoi(getenv("QB200_LANE_STEPS")) : 40;  // 0: warp per response only
         strip_count_kernel<<<grid_for((n_resp + 31) / 32), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts,
                                                                                  ts.cnt ? desc : nullptr, lane_steps);
-        LAUNCHED();
+        LAUNCHED("strip_count_kernel");
     }
     const int tb = 256;
     const unsigned rg = (unsigned)((n_req + tb - 1) / tb);
     request_layout_kernel<<<rg, tb, 0, stream>>>(in_off, req_off, n_req, klen, hide, sj, sep_len, dst, reqlen);
-    LAUNCHED();
+    LAUNCHED("request_layout_kernel");
     launch_scan(reqlen, n_req, out_off, (int64_t*)((uint8_t*)reqlen + align256((size_t)(n_req + 2) * 8)), stream);
     request_finalize_kernel<<<rg, tb, 0, stream>>>(req_off, n_req, out_off, dst);
-    LAUNCHED();
+    LAUNCHED("request_finalize_kernel");
     if (n_resp > 0) {
         strip_copy_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, dst,
                                                                     hide, sep, sep_len, out_bytes, resp_out_len,
                                                                     (hide && ts.cnt) ? desc : nullptr, ts);
-        LAUNCHED();
+        LAUNCHED("strip_copy_kernel");
     }
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
@@ -845,7 +883,7 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     if (n_streams == 0) {
         if (!chain) {
             set_i64_kernel<<<1, 1, 0, stream>>>(out_chunk_off, 0);
-            LAUNCHED();
+            LAUNCHED("set_i64_kernel");
         }
         CUDA_TRY(cudaGetLastError());
         return QB200_OK;
@@ -871,7 +909,7 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     stream_count_kernel<<<grid_for((n_streams + 31) / 32), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
                                                                                  n_streams, si, use_tokens ? so : nullptr, flags, totals,
                                                                                  ts, desc, sid, lane_steps);
-    LAUNCHED();
+    LAUNCHED("stream_count_kernel");
     // chained call: this call's output starts where out_chunk_off[first chunk of the call] says (written by the call before)
     launch_scan(totals, n_streams, bases, (int64_t*)((uint8_t*)bases + align256((size_t)(n_streams + 2) * 8)), stream,
                 chain ? out_chunk_off : nullptr, chain ? stream_off : nullptr);
@@ -880,14 +918,14 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
         if (nb > 148 * 64) nb = 148 * 64;
         if (nb < 1) nb = 1;
         stream_offsets_kernel<<<(unsigned)nb, 256, 0, stream>>>(chunk_off, stream_off, n_streams, bases, out_chunk_off, desc, sid);
-        LAUNCHED();
+        LAUNCHED("stream_offsets_kernel");
         stream_finish_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(
             tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, si, so, flags, bases, out_bytes, out_chunk_off, desc);
-        LAUNCHED();
+        LAUNCHED("stream_finish_kernel");
     } else {
         stream_copy_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
                                                                         n_streams, si, so, flags, bases, out_bytes, out_chunk_off);
-        LAUNCHED();
+        LAUNCHED("stream_copy_kernel");
     }
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
@@ -948,7 +986,7 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
     CUDA_TRY(cudaMemsetAsync(P.tile_state, 0, tile_scratch_bytes(max_tiles), stream));
     stream_tile_map_kernel<<<(unsigned)((n_streams + 255) / 256), 256, 0, stream>>>(chunk_off, n_chunks, stream_off, n_streams,
                                                                                    rec, max_tiles);
-    LAUNCHED();
+    LAUNCHED("stream_tile_map_kernel");
     static bool attr_set = false;
     if (!attr_set) {
         CUDA_TRY(cudaFuncSetAttribute(stream_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileShared)));
@@ -957,7 +995,7 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
     int64_t grid = 4 * (int64_t)sm_count();
     if (grid > max_tiles) grid = max_tiles;
     stream_tile_kernel<<<(unsigned)grid, kTileThreads, sizeof(TileShared), stream>>>(P);
-    LAUNCHED();
+    LAUNCHED("stream_tile_kernel");
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
 }
@@ -1040,7 +1078,7 @@ int qb200_sse_frame_batch(const uint8_t* in_bytes, const int64_t* in_off, int64_
     CUDA_TRY(cudaGetDeviceCount(&dev_count));
     if (n_items == 0) {
         set_i64_kernel<<<1, 1, 0, stream>>>(out_off, 0);
-        LAUNCHED();
+        LAUNCHED("set_i64_kernel");
         CUDA_TRY(cudaGetLastError());
         return QB200_OK;
     }
@@ -1050,11 +1088,11 @@ int qb200_sse_frame_batch(const uint8_t* in_bytes, const int64_t* in_off, int64_
     if (blocks > 148 * 32) blocks = 148 * 32;
     sse_count_kernel<<<(unsigned)blocks, 256, 0, stream>>>(in_bytes, in_off, n_items, item_prefix, prefix_off, suffix_len, flags,
                                                           lens);
-    LAUNCHED();
+    LAUNCHED("sse_count_kernel");
     launch_scan(lens, n_items, out_off, partial, stream);
     sse_write_kernel<<<(unsigned)blocks, 256, 0, stream>>>(in_bytes, in_off, n_items, item_prefix, prefix_bytes, prefix_off, suffix,
                                                           suffix_len, out_off, out_bytes);
-    LAUNCHED();
+    LAUNCHED("sse_write_kernel");
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
 }
@@ -1062,9 +1100,10 @@ int qb200_sse_frame_batch(const uint8_t* in_bytes, const int64_t* in_off, int64_
 int qb200_stream_flush_batch(qb200_stream_state* state, int64_t n_streams, void* stream_) {
     if (n_streams < 0 || (n_streams > 0 && !state)) return fail(QB200_EINVAL, "stream_flush_batch: bad argument");
     if (n_streams == 0) return QB200_OK;
-    stream_flush_kernel<<<(unsigned)((n_streams + 255) / 256), 256, 0, (cudaStream_t)stream_>>>(
+    cudaStream_t stream = (cudaStream_t)stream_;
+    stream_flush_kernel<<<(unsigned)((n_streams + 255) / 256), 256, 0, stream>>>(
         reinterpret_cast<StreamState*>(state), n_streams);
-    LAUNCHED();
+    LAUNCHED("stream_flush_kernel");
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
 }

@@ -146,6 +146,26 @@ int qb200_sse_frame_batch(const uint8_t *in_bytes, const int64_t *in_off, int64_
                           int32_t suffix_len, uint32_t flags, uint8_t *out_bytes, int64_t out_capacity, int64_t *out_off,
                           void *scratch, size_t scratch_bytes, void *stream);
 
+/* Aggregate-strategy prompt assembly, replaces the loop + join + template substitution of
+ * src/quorum/oai_proxy.py:406-423 over a batch of requests:
+ *   prompt[q] = head[q] + join_{i}(label[i] + response[req_off[q] + i], sep) + tail
+ * where the host renders head[q] = query_format.format(query=...) + (template text before "{responses}"), tail = the
+ * template text after it, label[i] = source_label_format.format(backend_name=f"LLM{i+1}") (n_labels = 0 when
+ * include_source_names is false; positions i >= n_labels get no label).  The responses are the already filtered contents
+ * (device buffer, e.g. the output of qb200_strip_concat_batch with one response per request).  head_off may be NULL (no
+ * heads).  All pointers are device pointers.  out_capacity >= sum of the prompt lengths; out_off has n_req + 1 entries. */
+size_t qb200_assemble_scratch_bytes(int64_t n_resp, int64_t n_req);
+int qb200_assemble_prompts_batch(const uint8_t *resp_bytes, const int64_t *resp_off, int64_t n_resp, const int64_t *req_off,
+                                 int64_t n_req, const uint8_t *head_bytes, const int64_t *head_off,
+                                 const uint8_t *label_bytes, const int32_t *label_off, int32_t n_labels, const uint8_t *sep,
+                                 int32_t sep_len, const uint8_t *tail, int32_t tail_len, uint8_t *out_bytes,
+                                 int64_t out_capacity, int64_t *out_off, void *scratch, size_t scratch_bytes, void *stream);
+
+/* Usage sums of the combined response (row f4), replaces src/quorum/oai_proxy.py:1298-1311: usage is [n_resp][3]
+ * (prompt_tokens, completion_tokens, total_tokens), out is [n_req][3], request q covers responses
+ * [req_off[q], req_off[q+1]).  Device pointers. */
+int qb200_usage_sums_batch(const int64_t *usage, const int64_t *req_off, int64_t n_req, int64_t *out, void *stream);
+
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 int64_t qb200_launch_count(void);
 

@@ -407,3 +407,27 @@ def concatenate(contents: List[str], separator: str, tags: List[str], hide_final
                 streaming: bool) -> str:
     return _dec(concatenate_bytes([_enc(c) for c in contents], _enc(separator), TagTable(tags),
                                   hide_final_think, streaming))
+
+
+def aggregate_prompt(source_responses: List[str], user_query: str, separator: str, include_original_query: bool = True,
+                     query_format: str = "Original query: {query}\n\n", include_source_names: bool = False,
+                     source_label_format: str = "Response from {backend_name}:\n",
+                     prompt_template: str = "You have received the following responses regarding the user's query:\n\n{responses}\n\nProvide a concise synthesis of these responses.") -> str:
+    """The aggregator prompt of src/quorum/oai_proxy.py:406-423 (row f3), restated: labels, join, template substitution."""
+    formatted = []
+    for i, response in enumerate(source_responses):  # :407-415
+        if include_source_names:
+            formatted.append(source_label_format.format(backend_name=f"LLM{i + 1}") + response)
+        else:
+            formatted.append(response)
+    intermediate = separator.join(formatted)  # :417
+    prompt = ""
+    if include_original_query:  # :419-421
+        prompt += query_format.format(query=user_query)
+    prompt += prompt_template.replace("{responses}", intermediate)  # :423
+    return prompt
+
+
+def usage_sums(usages: List[List[int]]) -> List[int]:
+    """oai_proxy.py:1298-1311 (row f4): the three sums over the successful responses of one request."""
+    return [sum(u[0] for u in usages), sum(u[1] for u in usages), sum(u[2] for u in usages)]

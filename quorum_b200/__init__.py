@@ -12,10 +12,11 @@ from .filter import (ThinkingTagFilter, ThinkingTagFilterBatch, strip_thinking_t
                      strip_thinking_tags_many)
 from .install import install, uninstall  # noqa: F401
 from .streaming import ConcatenateStreamSession, parse_sse_chunk  # noqa: F401
-from . import batch, sharding, sse  # noqa: F401
+from . import aggregate, batch, sharding, sse  # noqa: F401
+from .aggregate import AggregatePromptBuilder  # noqa: F401
 
 __all__ = [
     "strip_thinking_tags", "strip_thinking_tags_many", "ThinkingTagFilter", "ThinkingTagFilterBatch",
     "ConcatenateStrategy", "concatenate", "concatenate_many", "ConcatenateStreamSession", "parse_sse_chunk",
-    "install", "uninstall", "batch", "sharding", "sse", "QuorumB200Error", "launch_count",
+    "install", "uninstall", "batch", "sharding", "sse", "aggregate", "AggregatePromptBuilder", "QuorumB200Error", "launch_count",
 ]

@@ -20,6 +20,7 @@
 #include "qb_tok.cuh"
 #include "qb_lane.cuh"
 #include "qb_sse.cuh"
+#include "qb_agg.cuh"
 #include <stdlib.h>
 
 using namespace qb;
@@ -1093,6 +1094,69 @@ int qb200_sse_frame_batch(const uint8_t* in_bytes, const int64_t* in_off, int64_
     sse_write_kernel<<<(unsigned)blocks, 256, 0, stream>>>(in_bytes, in_off, n_items, item_prefix, prefix_bytes, prefix_off, suffix,
                                                           suffix_len, out_off, out_bytes);
     LAUNCHED("sse_write_kernel");
+    CUDA_TRY(cudaGetLastError());
+    return QB200_OK;
+}
+
+size_t qb200_assemble_scratch_bytes(int64_t n_resp, int64_t n_req) {
+    if (n_resp < 0) n_resp = 0;
+    if (n_req < 0) n_req = 0;
+    return 2 * align256((size_t)(n_resp + 2) * 8) + align256((size_t)(n_resp + 2) * 4) + align256((size_t)(n_req + 2) * 8) +
+           align256((size_t)(n_req / kScanSlice + 4) * 8) + 256;
+}
+
+int qb200_assemble_prompts_batch(const uint8_t* resp_bytes, const int64_t* resp_off, int64_t n_resp, const int64_t* req_off,
+                                 int64_t n_req, const uint8_t* head_bytes, const int64_t* head_off, const uint8_t* label_bytes,
+                                 const int32_t* label_off, int32_t n_labels, const uint8_t* sep, int32_t sep_len,
+                                 const uint8_t* tail, int32_t tail_len, uint8_t* out_bytes, int64_t out_capacity, int64_t* out_off,
+                                 void* scratch, size_t scratch_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!resp_off || !req_off || !out_off || n_resp < 0 || n_req < 0 || n_labels < 0 || sep_len < 0 || tail_len < 0 ||
+        out_capacity < 0 || (n_labels > 0 && (!label_bytes || !label_off)) || (sep_len > 0 && !sep) || (tail_len > 0 && !tail))
+        return fail(QB200_EINVAL, "assemble_prompts_batch: bad argument");
+    if (scratch_bytes < qb200_assemble_scratch_bytes(n_resp, n_req) || !scratch)
+        return fail(QB200_ESCRATCH, "assemble_prompts_batch: scratch too small (see qb200_assemble_scratch_bytes)");
+    if (n_req == 0) {
+        set_i64_kernel<<<1, 1, 0, stream>>>(out_off, 0);
+        LAUNCHED("set_i64_kernel");
+        CUDA_TRY(cudaGetLastError());
+        return QB200_OK;
+    }
+    uint8_t* sp = (uint8_t*)scratch;
+    int64_t* rel = (int64_t*)sp;
+    sp += align256((size_t)(n_resp + 2) * 8);
+    int64_t* req_of = (int64_t*)sp;
+    sp += align256((size_t)(n_resp + 2) * 8);
+    int32_t* idx = (int32_t*)sp;
+    sp += align256((size_t)(n_resp + 2) * 4);
+    int64_t* reqlen = (int64_t*)sp;
+    sp += align256((size_t)(n_req + 2) * 8);
+    int64_t* partial = (int64_t*)sp;
+    const unsigned rg = (unsigned)((n_req + 255) / 256);
+    assemble_layout_kernel<<<rg, 256, 0, stream>>>(resp_off, req_off, n_req, head_off, label_off, n_labels, sep_len, tail_len, rel,
+                                                  idx, reqlen);
+    LAUNCHED("assemble_layout_kernel");
+    assemble_owner_kernel<<<rg, 256, 0, stream>>>(req_off, n_req, req_of);
+    LAUNCHED("assemble_owner_kernel");
+    launch_scan(reqlen, n_req, out_off, partial, stream);
+    assemble_frame_kernel<<<(unsigned)((n_req + 7) / 8), 256, 0, stream>>>(req_off, n_req, head_bytes, head_off, tail, tail_len, out_off,
+                                                                          out_bytes);
+    LAUNCHED("assemble_frame_kernel");
+    if (n_resp > 0) {
+        assemble_copy_kernel<<<grid_for(n_resp), 256, 0, stream>>>(resp_bytes, resp_off, n_resp, rel, idx, req_of, label_bytes, label_off,
+                                                                  n_labels, sep, sep_len, out_off, out_bytes);
+        LAUNCHED("assemble_copy_kernel");
+    }
+    CUDA_TRY(cudaGetLastError());
+    return QB200_OK;
+}
+
+int qb200_usage_sums_batch(const int64_t* usage, const int64_t* req_off, int64_t n_req, int64_t* out, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (n_req < 0 || (n_req > 0 && (!usage || !req_off || !out))) return fail(QB200_EINVAL, "usage_sums_batch: bad argument");
+    if (n_req == 0) return QB200_OK;
+    usage_sums_kernel<<<(unsigned)((n_req + 255) / 256), 256, 0, stream>>>(usage, req_off, n_req, out);
+    LAUNCHED("usage_sums_kernel");
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
 }

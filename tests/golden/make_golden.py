@@ -129,8 +129,41 @@ def fold_tables():
     return out
 
 
+def aggregate_cases(q, rng):
+    """Prompts built by the reference's own aggregate_responses (oai_proxy.py:374-423): the aggregator call is replaced
+    by a stub that captures the request body, everything before it is the unmodified code."""
+    import asyncio
+    captured = {}
+
+    async def fake_call_backend(backend, body, headers, timeout=None):
+        captured["prompt"] = json.loads(body)["messages"][0]["content"]
+        return {"status_code": 200, "content": {"choices": [{"message": {"content": "synth"}}]}}
+
+    q.call_backend = fake_call_backend
+    seps = ["\n\n---\n\n", "\n", "", " § "]
+    templates = ["You have received the following responses regarding the user's query:\n\n{responses}\n\nProvide a concise synthesis of these responses.",
+                 "{responses}", "no placeholder at all", "A {responses} B {responses} C", "é{responses}日本"]
+    qfmts = ["Original query: {query}\n\n", "{query}", "Q={query!r}; "]
+    lfmts = ["Response from {backend_name}:\n", "[{backend_name}] ", ""]
+    cases = []
+    for _ in range(300):
+        tags = rng.choice(TAG_SETS)
+        responses = [rand_text(rng, tags, rng.randrange(0, 8)) if rng.random() > 0.1 else "" for _ in range(rng.randrange(0, 7))]
+        case = {"responses": responses, "query": rand_text(rng, tags, rng.randrange(0, 4)), "sep": rng.choice(seps),
+                "include_query": rng.random() < 0.7, "query_format": rng.choice(qfmts), "include_names": rng.random() < 0.5,
+                "label_format": rng.choice(lfmts), "template": rng.choice(templates)}
+        captured.clear()
+        asyncio.run(q.aggregate_responses(responses, {"model": "m", "url": "http://x"}, case["query"], case["sep"], case["include_query"],
+                                          case["query_format"], case["include_names"], case["label_format"], case["template"],
+                                          {"Authorization": "Bearer t"}))
+        case["expect"] = captured["prompt"]
+        cases.append(case)
+    return cases
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--aggregate-only", action="store_true", help="only (re)write aggregate_cases.json")
     ap.add_argument("--fuzz", type=int, default=0)
     ap.add_argument("--seed", type=int, default=20261106)
     ap.add_argument("--no-write", action="store_true")
@@ -138,6 +171,12 @@ def main():
     q = load_reference()
     rng = random.Random(args.seed)
     meta = {"python": sys.version, "generator": "tests/golden/make_golden.py", "seed": args.seed}
+    if args.aggregate_only:
+        cases = aggregate_cases(q, random.Random(args.seed + 1))
+        with open(os.path.join(HERE, "aggregate_cases.json"), "w") as f:
+            json.dump({"meta": meta, "cases": cases}, f, ensure_ascii=True, separators=(",", ":"))
+        print("wrote", len(cases), "aggregate cases")
+        return
 
     # hand-written seeds (observed behaviour) + random cases
     hand = [

@@ -43,7 +43,11 @@ __device__ __forceinline__ uint32_t lt_any16(const uint4& v) { return lt_any(v.x
 // "look at the candidates" branch serve two steps, and each lane has 64 bytes in flight.
 __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                                                        const int64_t* __restrict__ off, const int64_t* __restrict__ idx, int64_t n,
-                                                       uint8_t* __restrict__ cnt, uint32_t* __restrict__ rec, int64_t max_steps) {
+                                                       uint8_t* __restrict__ cnt, uint32_t* __restrict__ rec, int64_t max_steps,
+                                                       unsigned long long* __restrict__ zero, int64_t zero_words) {
+    // housekeeping for the kernel that follows on the stream: its look-back words and ticket start at zero
+    if (blockIdx.x == 0)
+        for (int64_t i = threadIdx.x; i < zero_words; i += blockDim.x) zero[i] = 0;
     const int lane = threadIdx.x & 31;
     const int half = lane >> 4;
     const unsigned hm = half ? 0xFFFF0000u : 0x0000FFFFu;  // the lanes of this lane's step

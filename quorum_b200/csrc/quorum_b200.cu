@@ -426,17 +426,42 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
 // A warp takes 32 consecutive streams, one per lane (qb_lane.cuh); streams that touch more than lane_steps steps, or do
 // not fit the descriptor, are then walked one at a time by the whole warp.  No tokens (QB200_PATH=general): the
 // byte-rescanning count of every stream.
+//
+// SCAN: the prefix sum over the streams' released bytes (their output bases) is done here as well, single pass: a block
+// takes 256 consecutive streams by ticket, scans its totals (warp shuffles + shared memory) and gets its base by
+// decoupled look-back over the blocks before it (lookback_exclusive, qb_tile.cuh; tickets give forward progress).
+// scan.state / scan.ticket are zeroed by the tokenizer kernel, which runs just before on the same stream.
+struct CountScan {
+    int64_t* bases;                 // out: bases[s]
+    unsigned long long* state;      // one look-back word per block of 256 streams
+    unsigned int* ticket;
+    const int64_t* init_arr;        // chained call: the first base is init_arr[*init_idx] (0 when null)
+    const int64_t* init_idx;
+};
+template <bool SCAN>
 __global__ void __launch_bounds__(kThreads, 4)
 stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                     const int64_t* __restrict__ chunk_off, int64_t n_chunks, const int64_t* __restrict__ stream_off,
                     int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
                     int64_t* __restrict__ totals, TokSrc ts, StreamDesc* __restrict__ desc, int32_t* __restrict__ sid,
-                    int lane_steps) {
+                    int lane_steps, CountScan scan) {
+    __shared__ int64_t s_wsum[kWarpsPerBlock];
+    __shared__ int64_t s_excl, s_ticket;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
     const int64_t cb = stream_off[0];
     const int64_t ngroups = (n_streams + 31) >> 5;
-    for (int64_t g = (int64_t)blockIdx.x * kWarpsPerBlock + wib; g < ngroups; g += (int64_t)gridDim.x * kWarpsPerBlock) {
+    int64_t init = 0;
+    if (SCAN && scan.init_arr) init = scan.init_arr[scan.init_idx ? *scan.init_idx : 0];
+    for (int64_t it = 0;; it++) {
+        int64_t t = (int64_t)blockIdx.x + it * gridDim.x;
+        if (SCAN) {
+            if (threadIdx.x == 0) s_ticket = (int64_t)atomicAdd(scan.ticket, 1u);
+            __syncthreads();
+            t = s_ticket;
+        }
+        if (t * kWarpsPerBlock >= ngroups) break;
+        const int64_t g = t * kWarpsPerBlock + wib;
         const int64_t s = (g << 5) + lane;
         const bool have = s < n_streams;
         int64_t c0 = 0, c1 = 0, tot = 0;
@@ -480,8 +505,32 @@ stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restric
             if (lane == j) tot = r.total_out;
             __syncwarp();
         }
-        if (have) totals[s] = tot;
-        if (sid) {  // chunk -> stream map of this call, for the offsets kernel: the group's chunks, stream by stream
+        if (!SCAN) {
+            if (have) totals[s] = tot;
+        } else {
+            int64_t incl = tot;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int64_t v = __shfl_up_sync(kFull, incl, d);
+                if (lane >= d) incl += v;
+            }
+            if (lane == 31) s_wsum[wib] = incl;
+            __syncthreads();
+            int64_t before = 0, block_tot = 0;
+#pragma unroll
+            for (int w = 0; w < kWarpsPerBlock; w++) {
+                const int64_t v = s_wsum[w];
+                if (w < wib) before += v;
+                block_tot += v;
+            }
+            if (wib == 0) {
+                const int64_t excl = lookback_exclusive(scan.state, t, block_tot, lane);
+                if (lane == 0) s_excl = excl;
+            }
+            __syncthreads();
+            if (have) scan.bases[s] = init + s_excl + before + incl - tot;
+        }
+        if (sid && g < ngroups) {  // chunk -> stream map of this call, for the offsets kernel: the group's chunks, stream by stream
             const int cnt = n_streams - (g << 5) < 32 ? (int)(n_streams - (g << 5)) : 32;
             for (int j = 0; j < cnt; j++) {
                 const int64_t d0 = __shfl_sync(kFull, c0, j), d1 = __shfl_sync(kFull, c1, j);
@@ -743,7 +792,8 @@ static size_t tok_scratch_bytes(int64_t byte_bound) {
 
 // tokenizer pass over the flat buffer; returns where the records are
 static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const int64_t* off, const int64_t* idx, int64_t n,
-                               int64_t byte_bound, uint8_t* scratch, cudaStream_t stream) {
+                               int64_t byte_bound, uint8_t* scratch, cudaStream_t stream, unsigned long long* zero = nullptr,
+                               int64_t zero_words = 0) {
     const int64_t st = steps_for(byte_bound);
     TokSrc ts;
     uint8_t* cnt = scratch;
@@ -752,7 +802,7 @@ static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const in
     const int64_t cap = 148 * 32;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    tokenize_kernel<<<(unsigned)blocks, 256, 0, stream>>>(tg, bytes, off, idx, n, cnt, rec, st);
+    tokenize_kernel<<<(unsigned)blocks, 256, 0, stream>>>(tg, bytes, off, idx, n, cnt, rec, st, zero, zero_words);
     LAUNCHED("tokenize_kernel");
     ts.cnt = cnt;
     ts.rec = rec;
@@ -898,22 +948,34 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     TokSrc ts;
     StreamDesc* desc = nullptr;
     size_t sid_offset = 0;
+    unsigned long long* scan_state = nullptr;
+    unsigned int* scan_ticket = nullptr;
     if (use_tokens) {  // descriptors + records (+ the chunk -> stream map) live behind the general + tile scratch regions
         uint8_t* tsp = (uint8_t*)scratch + stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity));
         desc = (StreamDesc*)tsp;
+        scan_state = (unsigned long long*)totals;  // (n_streams / 256 + 2) words + the ticket fit in the totals array
+        const int64_t nblk = (n_streams + 255) / 256 + 1;
+        scan_ticket = (unsigned int*)(scan_state + nblk);
         ts = launch_tokenizer(tags->dev, chunk_bytes, chunk_off, stream_off, n_streams, out_capacity,
-                              tsp + stream_desc_scratch_bytes(n_streams), stream);
+                              tsp + stream_desc_scratch_bytes(n_streams), stream, scan_state, nblk + 1);
         sid_offset = (size_t)(tsp - (uint8_t*)scratch) + stream_desc_scratch_bytes(n_streams) + tok_scratch_bytes(out_capacity);
     }
     int32_t* sid = use_tokens ? (int32_t*)((uint8_t*)scratch + sid_offset) : nullptr;
     static const int lane_steps = getenv("QB200_LANE_STEPS") ? atoi(getenv("QB200_LANE_STEPS")) : 40;  // 0: warp per stream only
-    stream_count_kernel<<<grid_for((n_streams + 31) / 32), kThreads, 0, stream>>>(tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off,
-                                                                                 n_streams, si, use_tokens ? so : nullptr, flags, totals,
-                                                                                 ts, desc, sid, lane_steps);
-    LAUNCHED("stream_count_kernel");
     // chained call: this call's output starts where out_chunk_off[first chunk of the call] says (written by the call before)
-    launch_scan(totals, n_streams, bases, (int64_t*)((uint8_t*)bases + align256((size_t)(n_streams + 2) * 8)), stream,
-                chain ? out_chunk_off : nullptr, chain ? stream_off : nullptr);
+    if (use_tokens) {  // prefix sum inside the count kernel (look-back words live where the totals would)
+        CountScan cs{bases, scan_state, scan_ticket, chain ? out_chunk_off : nullptr, chain ? stream_off : nullptr};
+        stream_count_kernel<true><<<grid_for((n_streams + 31) / 32), kThreads, 0, stream>>>(
+            tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, si, so, flags, totals, ts, desc, sid, lane_steps, cs);
+        LAUNCHED("stream_count_kernel");
+    } else {
+        stream_count_kernel<false><<<grid_for((n_streams + 31) / 32), kThreads, 0, stream>>>(
+            tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, si, nullptr, flags, totals, ts, desc, sid, lane_steps,
+            CountScan{});
+        LAUNCHED("stream_count_kernel");
+        launch_scan(totals, n_streams, bases, (int64_t*)((uint8_t*)bases + align256((size_t)(n_streams + 2) * 8)), stream,
+                    chain ? out_chunk_off : nullptr, chain ? stream_off : nullptr);
+    }
     if (use_tokens) {
         int64_t nb = (n_chunks + 1023) / 1024;
         if (nb > 148 * 64) nb = 148 * 64;

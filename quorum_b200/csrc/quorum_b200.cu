@@ -565,11 +565,12 @@ stream_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
 // hold intervals, carried bytes); what is left per boundary is a clamp-sum over at most kDescRuns runs and kDescHolds
 // interval tests.  A thread takes four consecutive boundaries (their loads are issued together; they nearly always share
 // one descriptor), threads are independent: no per-stream chain of dependent loads.
+template <int PER>
 __global__ void __launch_bounds__(256)
 stream_offsets_kernel(const int64_t* __restrict__ chunk_off, const int64_t* __restrict__ stream_off, int64_t n_streams,
                       const int64_t* __restrict__ bases, int64_t* __restrict__ out_chunk_off, const StreamDesc* __restrict__ desc,
                       const int32_t* __restrict__ sid) {
-    constexpr int PER = 4;  // boundaries per thread; a warp takes 32 * PER consecutive ones, lane-interleaved (coalesced)
+    // PER boundaries per thread; a warp takes 32 * PER consecutive ones, lane-interleaved (coalesced)
     const int64_t cb = stream_off[0], nb = stream_off[n_streams] - cb;  // boundary cb + 1 + i ends chunk cb + i, i < nb
     if (blockIdx.x == 0 && threadIdx.x == 0) out_chunk_off[cb] = bases[0];
     const int64_t* co = chunk_off + cb + 1;
@@ -977,10 +978,11 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
                     chain ? out_chunk_off : nullptr, chain ? stream_off : nullptr);
     }
     if (use_tokens) {
-        int64_t nb = (n_chunks + 1023) / 1024;
+        constexpr int kPer = 8;  // boundaries per thread (measured: 1 -> 606, 2 -> 588, 4 -> 565, 8 -> 563 us per cfg2 call)
+        int64_t nb = (n_chunks + 256 * kPer - 1) / (256 * kPer);
         if (nb > 148 * 64) nb = 148 * 64;
         if (nb < 1) nb = 1;
-        stream_offsets_kernel<<<(unsigned)nb, 256, 0, stream>>>(chunk_off, stream_off, n_streams, bases, out_chunk_off, desc, sid);
+        stream_offsets_kernel<kPer><<<(unsigned)nb, 256, 0, stream>>>(chunk_off, stream_off, n_streams, bases, out_chunk_off, desc, sid);
         LAUNCHED("stream_offsets_kernel");
         stream_finish_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(
             tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, si, so, flags, bases, out_bytes, out_chunk_off, desc);

@@ -111,6 +111,8 @@ __device__ __noinline__ void stream_copy_slow(const DevTags& tg, const uint8_t* 
 // ---------------------------------------------------------------------------------------------------------------
 // kernels: strip + concat
 // ---------------------------------------------------------------------------------------------------------------
+constexpr int kOffsetsPer = 8;                    // boundaries per thread in stream_offsets_kernel
+constexpr int kOffsetsTile = 32 * kOffsetsPer;   // boundaries per warp there
 constexpr int kWarpsPerBlock = 8;
 constexpr int kThreads = kWarpsPerBlock * 32;
 
@@ -530,13 +532,10 @@ stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restric
             __syncthreads();
             if (have) scan.bases[s] = init + s_excl + before + incl - tot;
         }
-        if (sid && g < ngroups) {  // chunk -> stream map of this call, for the offsets kernel: the group's chunks, stream by stream
-            const int cnt = n_streams - (g << 5) < 32 ? (int)(n_streams - (g << 5)) : 32;
-            for (int j = 0; j < cnt; j++) {
-                const int64_t d0 = __shfl_sync(kFull, c0, j), d1 = __shfl_sync(kFull, c1, j);
-                const int32_t sv = (int32_t)((g << 5) + j);
-                for (int64_t k = d0 + lane; k < d1; k += 32) sid[k - cb] = sv;
-            }
+        if (sid && have && c1 > c0) {
+            // tile -> stream map for the offsets kernel: the stream that owns the first boundary of every tile of
+            // kOffsetsTile boundaries (boundary cb + 1 + i ends chunk cb + i).  A lane marks the tiles that start in its chunks.
+            for (int64_t w = (c0 - cb + kOffsetsTile - 1) / kOffsetsTile; cb + w * kOffsetsTile < c1; w++) sid[w] = (int32_t)s;
         }
     }
 }
@@ -583,8 +582,33 @@ stream_offsets_kernel(const int64_t* __restrict__ chunk_off, const int64_t* __re
 #pragma unroll
         for (int j = 0; j < PER; j++) {
             const int64_t i = i0 + 32 * j;
-            sv[j] = i < nb ? sid[i] : -1;
             pos[j] = i < nb ? co[i] : 0;
+        }
+        // which stream owns each boundary: start from the owner of the tile's first boundary (written by the count
+        // kernel) and step over the stream ends in between (a tile usually lies inside one or two streams)
+        int sc = sid[(i0 - lane) / (32 * PER)];
+#pragma unroll
+        for (int j = 0; j < PER; j++) {
+            const int64_t i = i0 + 32 * j;
+            sv[j] = -1;
+            if (i < nb) {
+                const int64_t k = cb + i;  // chunk index
+                int steps = 0;
+                while (k >= stream_off[sc + 1]) {
+                    sc++;
+                    if (++steps == 16) {  // many short or empty streams: binary search for the last stream starting at or before k
+                        int64_t lo = sc, hi = n_streams - 1;
+                        while (lo < hi) {
+                            const int64_t mid = (lo + hi + 1) >> 1;
+                            if (stream_off[mid] <= k) lo = mid;
+                            else hi = mid - 1;
+                        }
+                        sc = (int)lo;
+                        break;
+                    }
+                }
+                sv[j] = sc;
+            }
         }
         int prev = -1, nruns = 0, held_kept = 0;
         int64_t ustart = 0, base = 0;
@@ -901,7 +925,7 @@ static int64_t tiles_for(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte
 // per tile: look-back state word + TileRec; plus the ticket
 static size_t tile_scratch_bytes(int64_t max_tiles) { return align256((size_t)(max_tiles + 1) * (8 + sizeof(TileRec)) + 64); }
 
-static size_t sid_scratch_bytes(int64_t n_chunks) { return align256((size_t)((n_chunks < 0 ? 0 : n_chunks) + 32) * 4); }
+static size_t sid_scratch_bytes(int64_t n_chunks) { return align256((size_t)((n_chunks < 0 ? 0 : n_chunks) / kOffsetsTile + 32) * 4); }
 
 size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity) {
     return stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity)) +
@@ -978,11 +1002,12 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
                     chain ? out_chunk_off : nullptr, chain ? stream_off : nullptr);
     }
     if (use_tokens) {
-        constexpr int kPer = 8;  // boundaries per thread (measured: 1 -> 606, 2 -> 588, 4 -> 565, 8 -> 563 us per cfg2 call)
-        int64_t nb = (n_chunks + 256 * kPer - 1) / (256 * kPer);
+        // boundaries per thread measured on cfg2: 1 -> 606, 2 -> 588, 4 -> 565, 8 -> 563 us per call
+        int64_t nb = (n_chunks + 256 * kOffsetsPer - 1) / (256 * kOffsetsPer);
         if (nb > 148 * 64) nb = 148 * 64;
         if (nb < 1) nb = 1;
-        stream_offsets_kernel<kPer><<<(unsigned)nb, 256, 0, stream>>>(chunk_off, stream_off, n_streams, bases, out_chunk_off, desc, sid);
+        stream_offsets_kernel<kOffsetsPer><<<(unsigned)nb, 256, 0, stream>>>(chunk_off, stream_off, n_streams, bases, out_chunk_off, desc,
+                                                                            sid);
         LAUNCHED("stream_offsets_kernel");
         stream_finish_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(
             tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, si, so, flags, bases, out_bytes, out_chunk_off, desc);

@@ -235,6 +235,31 @@ def test_fuzz_stream_vs_oracle(qb, dev, tags):
         _check_stream(qb, dev, tags, data, chunk_off, stream_off, None, flush)
 
 
+def test_stream_ownership_many_short_and_empty_streams(qb, dev):
+    """Shapes that stress the boundary -> stream lookup of the offsets kernel: one chunk per stream (a serving step
+    that feeds one delta to every stream), and long runs of chunk-free streams between the ones that have chunks."""
+    import random
+    from quorum_b200 import synth
+    tags = synth.TAGS5
+    rng = random.Random(21)
+    texts = [b"a<thi", b"nk>x</think>b ", b"plain text ", b"<think>", b"</think> ok", b"", b"<", b"x" * 70]
+    # (1) one chunk per stream
+    chunks = [rng.choice(texts) for _ in range(6000)]
+    data, chunk_off = synth.pack(chunks)
+    _check_stream(qb, dev, tags, data, chunk_off, np.arange(len(chunks) + 1, dtype=np.int64), None, False)
+    # (2) mostly chunk-free streams, runs of up to 200 of them in a row
+    chunks, stream_off = [], [0]
+    while len(stream_off) < 30000:
+        for _ in range(rng.randrange(0, 200)):
+            stream_off.append(len(chunks))
+        for _ in range(rng.randrange(1, 4)):
+            chunks.append(rng.choice(texts))
+        stream_off.append(len(chunks))
+    data, chunk_off = synth.pack(chunks)
+    for flush in (False, True):
+        _check_stream(qb, dev, tags, data, chunk_off, np.asarray(stream_off, dtype=np.int64), None, flush)
+
+
 def test_stream_incremental_launches_vs_oracle(qb, dev):
     """Feed the same streams in 1, 2, 5 launches with state carried on the device: outputs concatenate identically."""
     import random

@@ -166,7 +166,15 @@ __device__ __forceinline__ int fast_match_tag(const DevTags& tg, const uint8_t* 
         cls = tg.cls_base[i];
         return 1 + is_close + L;
     }
-    if ((b0 | b1 | b2 | b3 | b4 | b5) & 0x80808080u) {  // possible U+0130/0131/212A/017F spelling: exact matcher
+    // A spelling the word compare cannot see uses U+0130/U+0131 (C4 B0/B1), U+017F (C5 BF) or U+212A (E2 84 AA): only a
+    // window that holds one of those lead bytes goes to the exact matcher (other multi-byte text cannot be part of a tag)
+    auto has_byte = [](uint32_t w, uint32_t pat) { const uint32_t v = w ^ pat; return (v - 0x01010101u) & ~v & 0x80808080u; };
+    // (w, nx: a word and the one after it; E2 counts only when 84 follows, which keeps typographic punctuation E2 80 xx out)
+    auto fold_lead = [&](uint32_t w, uint32_t nx) {
+        return has_byte(w & 0xFEFEFEFEu, 0xC4C4C4C4u) | (has_byte(w, 0xE2E2E2E2u) & has_byte(__funnelshift_r(w, nx, 8), 0x84848484u));
+    };
+    if (((b0 | b1 | b2 | b3 | b4 | b5) & 0x80808080u) &&
+        (fold_lead(b0, b1) | fold_lead(b1, b2) | fold_lead(b2, b3) | fold_lead(b3, b4) | fold_lead(b4, b5) | fold_lead(b5, 0x84848484u))) {
         const PtrAcc A{D};
         int64_t ex;
         int64_t tend = match_tag(tg, A, x, end, is_close != 0, cls, ex);

@@ -40,7 +40,7 @@ extern "C" {
 #define QB200_STREAM_JOIN 2u /* strip_concat: streaming-final join, drop inputs that are empty BEFORE the filter (oai_proxy.py:760-764) */
 #define QB200_FLUSH 4u       /* stream_feed: apply ThinkingTagFilter.flush() after the last chunk (oai_proxy.py:739, 352-371) */
 #define QB200_SKIP_EMPTY 16u /* sse_frame: items with empty content produce no event (`if safe_text`, oai_proxy.py:625-628) */
-#define QB200_CHAIN 8u       /* stream_feed: this call is one slice of a larger batch, see qb200_stream_feed_batch */
+#define QB200_CHAIN 8u       /* this call is one slice of a larger batch, see qb200_stream_feed_batch / qb200_strip_concat_batch */
 
 typedef struct qb200_tags qb200_tags; /* opaque, host-side */
 
@@ -80,7 +80,12 @@ void qb200_tags_destroy(qb200_tags *tags);
  * strip_thinking_tags.  Without QB200_HIDE the bytes are copied unchanged (hide flag False, oai_proxy.py:134-135).
  * Outputs: request q's text is out_bytes[out_off[q] .. out_off[q+1]) (out_off has n_req+1 entries, out_off[0]=0);
  * resp_out_len (optional, n_resp entries) receives each response's filtered length (0 for excluded ones).
- * out_capacity must be >= in_off[n_resp] + sep_len * n_resp.   in_bytes and out_bytes must be 16-byte aligned. */
+ * out_capacity must be >= in_off[n_resp] + sep_len * n_resp.   in_bytes and out_bytes must be 16-byte aligned.
+ * QB200_CHAIN feeds one large batch slice by slice (to overlap host<->device copies with compute): in_bytes and
+ * out_bytes stay those of the whole batch, `in_off` points at the slice's first response (entries still absolute byte
+ * offsets), `req_off` holds the slice's requests as response indices relative to that first response, `out_off` points at
+ * the slice's first request and out_off[0] already holds where the slice's output starts (the previous slice's call wrote
+ * it; the first slice is called without the flag).  Slices are issued in order on one stream. */
 size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req, int64_t out_capacity);
 int qb200_strip_concat_batch(const qb200_tags *tags, const uint8_t *in_bytes, const int64_t *in_off, int64_t n_resp,
                              const int64_t *req_off, int64_t n_req, const uint8_t *sep, int32_t sep_len,

@@ -84,12 +84,13 @@ def strip_concat_batch(tags: TagTable, in_bytes: torch.Tensor, in_off: torch.Ten
                        req_off: Optional[torch.Tensor], sep: Optional[torch.Tensor], *, hide: bool, streaming: bool,
                        out_bytes: Optional[torch.Tensor] = None, out_off: Optional[torch.Tensor] = None,
                        resp_out_len: Optional[torch.Tensor] = None, scratch: Optional[torch.Tensor] = None,
-                       want_resp_len: bool = False):
+                       want_resp_len: bool = False, chain: bool = False):
     """strip_thinking_tags over every response + the concatenate join per request (qb200_strip_concat_batch).
 
     in_bytes: uint8[total]; in_off: int64[n_resp+1]; req_off: int64[n_req+1] or None (one response per request);
     sep: uint8[sep_len] device tensor (for the streaming-final join pass "\\n"+separator, oai_proxy.py:841).
     Returns (out_bytes, out_off, resp_out_len or None); request q is out_bytes[out_off[q]:out_off[q+1]].
+    chain=True (QB200_CHAIN): this call is one slice of a larger batch, see include/quorum_b200.h.
     Nothing is synchronised: results are ordered on the current stream.
     """
     dev = in_off.device
@@ -114,7 +115,7 @@ def strip_concat_batch(tags: TagTable, in_bytes: torch.Tensor, in_off: torch.Ten
         need = lib().qb200_strip_concat_scratch_bytes(n_resp, n_req, out_bytes.numel())
         if scratch is None or scratch.numel() < need:
             scratch = torch.empty(need, dtype=torch.uint8, device=dev)
-        flags = (QB200_HIDE if hide else 0) | (QB200_STREAM_JOIN if streaming else 0)
+        flags = (QB200_HIDE if hide else 0) | (QB200_STREAM_JOIN if streaming else 0) | (QB200_CHAIN if chain else 0)
         check(lib().qb200_strip_concat_batch(
             tags.handle, _ptr(in_bytes), _ptr(in_off), n_resp, _ptr(req_off), n_req, _ptr(sep), sep_len, flags,
             _ptr(out_bytes), out_bytes.numel(), _ptr(out_off), _ptr(resp_out_len), _ptr(scratch), scratch.numel(),
@@ -315,7 +316,7 @@ class HostStripConcat:
         self.sep = torch.frombuffer(bytearray(sep), dtype=torch.uint8).to(d) if sep else None
         self.d_data = torch.empty(max_bytes, dtype=torch.uint8, device=d)
         self.d_io = torch.empty(max_resp + 1, dtype=torch.int64, device=d)
-        self.d_ro = torch.empty(max_req + 1, dtype=torch.int64, device=d)
+        self.d_ro = torch.empty(max_req + 64, dtype=torch.int64, device=d)  # every slice of run() has its own rebased copy
         self.d_out = torch.empty(max_bytes + len(sep) * max_resp + 16, dtype=torch.uint8, device=d)
         self.d_oo = torch.empty(max_req + 1, dtype=torch.int64, device=d)
         self.d_scratch = torch.empty(lib().qb200_strip_concat_scratch_bytes(max_resp, max_req, self.d_out.numel()),
@@ -323,17 +324,69 @@ class HostStripConcat:
         self.h_out = torch.empty(self.d_out.numel(), dtype=torch.uint8).pin_memory()
         self.h_oo = torch.empty(max_req + 1, dtype=torch.int64).pin_memory()
 
-    def run(self, h_data: torch.Tensor, h_in_off: torch.Tensor, h_req_off: torch.Tensor, *, hide: bool, streaming: bool):
+    def run(self, h_data: torch.Tensor, h_in_off: torch.Tensor, h_req_off: torch.Tensor, *, hide: bool, streaming: bool,
+            slices: int = 8):
+        """Returns (h2d_bytes, d2h_bytes); results are in self.h_out[: self.h_oo[n_req]] and self.h_oo.
+
+        The batch is processed in `slices` slices of requests (QB200_CHAIN) on three streams: the upload of slice k+1,
+        the kernels of slice k and the download of slice k-1 overlap, so the call costs about max(upload, download)."""
         nb, nr, nq = h_data.numel(), h_in_off.numel() - 1, h_req_off.numel() - 1
-        data, io, ro = self.d_data[:nb], self.d_io[:nr + 1], self.d_ro[:nq + 1]
-        data.copy_(h_data, non_blocking=True)
-        io.copy_(h_in_off, non_blocking=True)
-        ro.copy_(h_req_off, non_blocking=True)
-        strip_concat_batch(self.tags, data, io, ro, self.sep, hide=hide, streaming=streaming, out_bytes=self.d_out,
-                           out_off=self.d_oo[:nq + 1], scratch=self.d_scratch)
-        self.h_oo[:nq + 1].copy_(self.d_oo[:nq + 1], non_blocking=True)
-        torch.cuda.current_stream(self.dev).synchronize()
+        if nq < 4 * slices or nb < (1 << 22):
+            slices = 1
+        dev = self.dev
+        cur = torch.cuda.current_stream(dev)
+        if not hasattr(self, "_s_in"):
+            self._s_in, self._s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+            self.h_ro = torch.empty(self.d_ro.numel(), dtype=torch.int64).pin_memory()
+        s_in, s_out = self._s_in, self._s_out
+        s_in.wait_stream(cur)
+        s_out.wait_stream(cur)
+        data, io, ro, oo = self.d_data[:nb], self.d_io[:nr + 1], self.d_ro, self.d_oo[:nq + 1]
+        qb_ = [nq * k // slices for k in range(slices + 1)]                    # request bounds
+        rb = [int(h_req_off[q]) for q in qb_]                                  # response bounds
+        bb = [int(h_in_off[r]) for r in rb]                                    # byte bounds
+        # a slice's requests as response indices relative to the slice's first response (one entry shared by neighbours
+        # would need two values, so every slice gets its own nq_k + 1 entries)
+        h_ro, pos, ro_at = self.h_ro, 0, []
+        for k in range(slices):
+            m = qb_[k + 1] - qb_[k] + 1
+            torch.sub(h_req_off[qb_[k]:qb_[k + 1] + 1], rb[k], out=h_ro[pos:pos + m])
+            ro_at.append((pos, m))
+            pos += m
+        ev_o, pending = [], None
+
+        def drain(k):                                                          # slice k's bytes -> host, once its end is known
+            ev_o[k].synchronize()
+            o0 = 0 if k == 0 else int(self.h_oo[qb_[k]])
+            o1 = int(self.h_oo[qb_[k + 1]])
+            with torch.cuda.stream(s_out):
+                self.h_out[o0:o1].copy_(self.d_out[o0:o1], non_blocking=True)
+
+        for k in range(slices):
+            p0, m = ro_at[k]
+            with torch.cuda.stream(s_in):
+                data[bb[k]:bb[k + 1]].copy_(h_data[bb[k]:bb[k + 1]], non_blocking=True)
+                io[rb[k]:rb[k + 1] + 1].copy_(h_in_off[rb[k]:rb[k + 1] + 1], non_blocking=True)
+                ro[p0:p0 + m].copy_(h_ro[p0:p0 + m], non_blocking=True)
+                ev_in = torch.cuda.Event()
+                ev_in.record(s_in)
+            cur.wait_event(ev_in)
+            strip_concat_batch(self.tags, data, io[rb[k]:rb[k + 1] + 1], ro[p0:p0 + m], self.sep, hide=hide, streaming=streaming,
+                               out_bytes=self.d_out, out_off=oo[qb_[k]:qb_[k + 1] + 1], scratch=self.d_scratch, chain=k > 0)
+            ev_c = torch.cuda.Event()
+            ev_c.record(cur)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_c)
+                lo = qb_[k] + (1 if k else 0)
+                self.h_oo[lo:qb_[k + 1] + 1].copy_(oo[lo:qb_[k + 1] + 1], non_blocking=True)
+                e = torch.cuda.Event()
+                e.record(s_out)
+                ev_o.append(e)
+            if pending is not None:
+                drain(pending)
+            pending = k
+        drain(pending)
+        s_out.synchronize()
+        cur.wait_stream(s_out)
         total = int(self.h_oo[nq])
-        self.h_out[:total].copy_(self.d_out[:total], non_blocking=True)
-        torch.cuda.current_stream(self.dev).synchronize()
         return nb + 8 * (nr + 1) + 8 * (nq + 1), total + 8 * (nq + 1)

@@ -870,7 +870,9 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
         return fail(QB200_ESCRATCH, "strip_concat_batch: scratch too small (see qb200_strip_concat_scratch_bytes)");
     int dev_count = 0;
     CUDA_TRY(cudaGetDeviceCount(&dev_count));
+    const bool chain = (flags & QB200_CHAIN) != 0;  // out_off[0] already holds where this call's output starts
     if (n_req == 0) {
+        if (chain) return QB200_OK;
         set_i64_kernel<<<1, 1, 0, stream>>>(out_off, 0);
         LAUNCHED("set_i64_kernel");
         CUDA_TRY(cudaGetLastError());
@@ -902,7 +904,8 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     const unsigned rg = (unsigned)((n_req + tb - 1) / tb);
     request_layout_kernel<<<rg, tb, 0, stream>>>(in_off, req_off, n_req, klen, hide, sj, sep_len, dst, reqlen);
     LAUNCHED("request_layout_kernel");
-    launch_scan(reqlen, n_req, out_off, (int64_t*)((uint8_t*)reqlen + align256((size_t)(n_req + 2) * 8)), stream);
+    launch_scan(reqlen, n_req, out_off, (int64_t*)((uint8_t*)reqlen + align256((size_t)(n_req + 2) * 8)), stream,
+                chain ? out_off : nullptr, nullptr);
     request_finalize_kernel<<<rg, tb, 0, stream>>>(req_off, n_req, out_off, dst);
     LAUNCHED("request_finalize_kernel");
     if (n_resp > 0) {

@@ -195,3 +195,28 @@ def test_chained_slices_and_pipelined_host_feeder(qb):
         assert np.array_equal(feeder.h_out[: int(exp_oco[-1])].numpy(), exp_out), slices
         st = feeder.d_state[:640].cpu().numpy().reshape(-1).view(c_oracle.STATE_DTYPE)
         assert np.array_equal(st["depth"], exp_st["depth"]) and np.array_equal(st["held_len"], exp_st["held_len"])
+
+
+def test_chained_slices_and_pipelined_host_strip_concat(qb):
+    """QB200_CHAIN on strip + concat: the host-buffer session processes the batch in slices of requests on three streams;
+    bytes and request offsets equal those of one call (ragged requests, multi-byte separator, both join forms)."""
+    from oracle import c_oracle
+    from quorum_b200 import synth
+    dev = torch.device("cuda", 0)
+    units = synth.cfg5_units(6 << 20, seed=31)
+    data, in_off = synth.pack(units)
+    rng = np.random.default_rng(7)
+    cuts = np.unique(np.concatenate([[0, len(units)], rng.integers(0, len(units), len(units) // 3)])).astype(np.int64)
+    sep = synth.SEP_MULTIBYTE.encode()
+    sess = qb.batch.HostStripConcat(qb.batch.tag_table(synth.TAGS5), dev, data.size, len(units), len(cuts) - 1, sep)
+    pin = lambda a: torch.from_numpy(np.array(a, copy=True)).pin_memory()  # noqa: E731
+    for streaming in (False, True):
+        flags = c_oracle.FLAG_HIDE | (c_oracle.FLAG_STREAM_JOIN if streaming else 0)
+        exp_out, exp_off, _ = c_oracle.strip_concat_batch(c_oracle.Tags(synth.TAGS5), data, in_off, cuts, sep, flags)
+        for slices in (1, 3, 8):
+            sess.h_out.zero_()
+            sess.h_oo.zero_()
+            sess.run(pin(data), pin(in_off), pin(cuts), hide=True, streaming=streaming, slices=slices)
+            torch.cuda.synchronize()
+            assert np.array_equal(sess.h_oo[: len(exp_off)].numpy(), exp_off), (streaming, slices)
+            assert np.array_equal(sess.h_out[: int(exp_off[-1])].numpy(), exp_out), (streaming, slices)

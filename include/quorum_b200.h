@@ -151,6 +151,26 @@ int qb200_sse_frame_batch(const uint8_t *in_bytes, const int64_t *in_off, int64_
                           int32_t suffix_len, uint32_t flags, uint8_t *out_bytes, int64_t out_capacity, int64_t *out_off,
                           void *scratch, size_t scratch_bytes, void *stream);
 
+/* SSE input parsing, replaces what src/quorum/oai_proxy.py:578-617 does with every HTTP chunk
+ * of a backend's stream before the filter: strict UTF-8 decode of the chunk (a chunk that does not decode has no events),
+ * .strip().split("\n\n"), startswith("data: "), [6:].strip(), "[DONE]", json.loads, choices[0].delta.content.
+ * Two calls, because the number of events is only known after the first:
+ *   qb200_sse_split_batch  -> ev_first[c] = index of chunk c's first event, ev_first[n_http] = number of events
+ *   (the host reads that one value, sizes out_off / ev_kind, and calls)
+ *   qb200_sse_parse_batch  -> one entry per event, in order: ev_kind[k] = 0 no delta, 1 delta (its JSON-unescaped content
+ *   is out_bytes[out_off[k] .. out_off[k+1]); lone surrogates in their 3-byte form), 2 the host must decide (anything
+ *   that is not certainly valid and well-typed under CPython's json module: there the reference's behaviour is Python's
+ *   exception semantics); *n_host (device) = number of kind-2 events.  Events of kind 0 and 2 have empty content, so
+ *   (out_bytes, out_off) can go to qb200_stream_feed_batch as (chunk_bytes, chunk_off) directly when *n_host is 0.
+ * out_capacity >= http_off[n_http] (unescaping never grows a string).  All pointers are device pointers. */
+size_t qb200_sse_split_scratch_bytes(int64_t n_http);
+int qb200_sse_split_batch(const uint8_t *http_bytes, const int64_t *http_off, int64_t n_http, int64_t *ev_first, void *scratch,
+                          size_t scratch_bytes, void *stream);
+size_t qb200_sse_parse_scratch_bytes(int64_t n_events);
+int qb200_sse_parse_batch(const uint8_t *http_bytes, const int64_t *http_off, int64_t n_http, const int64_t *ev_first,
+                          int64_t n_events, uint8_t *out_bytes, int64_t out_capacity, int64_t *out_off, uint8_t *ev_kind,
+                          int64_t *n_host, void *scratch, size_t scratch_bytes, void *stream);
+
 /* Aggregate-strategy prompt assembly, replaces the loop + join + template substitution of
  * src/quorum/oai_proxy.py:406-423 over a batch of requests:
  *   prompt[q] = head[q] + join_{i}(label[i] + response[req_off[q] + i], sep) + tail

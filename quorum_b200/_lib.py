@@ -18,6 +18,7 @@ EXPORTS = [
     "qb200_stream_flush_batch", "qb200_launch_count", "qb200_stream_feed_batch_noalloc",
     "qb200_sse_frame_scratch_bytes", "qb200_sse_frame_batch", "qb200_profile_begin", "qb200_profile_end",
     "qb200_assemble_scratch_bytes", "qb200_assemble_prompts_batch", "qb200_usage_sums_batch",
+    "qb200_sse_split_scratch_bytes", "qb200_sse_split_batch", "qb200_sse_parse_scratch_bytes", "qb200_sse_parse_batch",
 ]
 NOALLOC_MAX_STREAMS = 65536
 
@@ -64,6 +65,14 @@ def lib() -> ctypes.CDLL:
     L.qb200_assemble_prompts_batch.argtypes = [vp, vp, i64, vp, i64, vp, vp, vp, vp, i32, vp, i32, vp, i32, vp, i64, vp, vp, sz, vp]
     L.qb200_usage_sums_batch.restype = ctypes.c_int
     L.qb200_usage_sums_batch.argtypes = [vp, vp, i64, vp, vp]
+    L.qb200_sse_split_scratch_bytes.restype = sz
+    L.qb200_sse_split_scratch_bytes.argtypes = [i64]
+    L.qb200_sse_split_batch.restype = ctypes.c_int
+    L.qb200_sse_split_batch.argtypes = [vp, vp, i64, vp, vp, sz, vp]
+    L.qb200_sse_parse_scratch_bytes.restype = sz
+    L.qb200_sse_parse_scratch_bytes.argtypes = [i64]
+    L.qb200_sse_parse_batch.restype = ctypes.c_int
+    L.qb200_sse_parse_batch.argtypes = [vp, vp, i64, vp, i64, vp, i64, vp, vp, vp, vp, sz, vp]
     L.qb200_profile_begin.restype = ctypes.c_int
     L.qb200_profile_begin.argtypes = [vp]
     L.qb200_profile_end.restype = i32

@@ -21,6 +21,7 @@
 #include "qb_lane.cuh"
 #include "qb_sse.cuh"
 #include "qb_agg.cuh"
+#include "qb_ssein.cuh"
 #include <stdlib.h>
 
 using namespace qb;
@@ -1186,6 +1187,73 @@ int qb200_sse_frame_batch(const uint8_t* in_bytes, const int64_t* in_off, int64_
     sse_write_kernel<<<(unsigned)blocks, 256, 0, stream>>>(in_bytes, in_off, n_items, item_prefix, prefix_bytes, prefix_off, suffix,
                                                           suffix_len, out_off, out_bytes);
     LAUNCHED("sse_write_kernel");
+    CUDA_TRY(cudaGetLastError());
+    return QB200_OK;
+}
+
+size_t qb200_sse_split_scratch_bytes(int64_t n_http) {
+    if (n_http < 0) n_http = 0;
+    return align256((size_t)(n_http + 2) * 8) + align256((size_t)(n_http / kScanSlice + 4) * 8) + 256;
+}
+
+int qb200_sse_split_batch(const uint8_t* http_bytes, const int64_t* http_off, int64_t n_http, int64_t* ev_first, void* scratch,
+                          size_t scratch_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!http_off || !ev_first || n_http < 0) return fail(QB200_EINVAL, "sse_split_batch: bad argument");
+    if (scratch_bytes < qb200_sse_split_scratch_bytes(n_http) || !scratch) return fail(QB200_ESCRATCH, "sse_split_batch: scratch too small");
+    if (n_http == 0) {
+        set_i64_kernel<<<1, 1, 0, stream>>>(ev_first, 0);
+        LAUNCHED("set_i64_kernel");
+        CUDA_TRY(cudaGetLastError());
+        return QB200_OK;
+    }
+    int64_t* counts = (int64_t*)scratch;
+    int64_t* partial = (int64_t*)((uint8_t*)scratch + align256((size_t)(n_http + 2) * 8));
+    sse_split_count_kernel<<<(unsigned)((n_http + 127) / 128), 128, 0, stream>>>(http_bytes, http_off, n_http, counts);
+    LAUNCHED("sse_split_count_kernel");
+    launch_scan(counts, n_http, ev_first, partial, stream);
+    CUDA_TRY(cudaGetLastError());
+    return QB200_OK;
+}
+
+size_t qb200_sse_parse_scratch_bytes(int64_t n_events) {
+    if (n_events < 0) n_events = 0;
+    return 5 * align256((size_t)(n_events + 2) * 8) + align256((size_t)(n_events / kScanSlice + 4) * 8) + 256;
+}
+
+int qb200_sse_parse_batch(const uint8_t* http_bytes, const int64_t* http_off, int64_t n_http, const int64_t* ev_first,
+                          int64_t n_events, uint8_t* out_bytes, int64_t out_capacity, int64_t* out_off, uint8_t* ev_kind,
+                          int64_t* n_host, void* scratch, size_t scratch_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!http_off || !ev_first || !out_off || !n_host || n_http < 0 || n_events < 0 || out_capacity < 0 || (n_events > 0 && !ev_kind))
+        return fail(QB200_EINVAL, "sse_parse_batch: bad argument");
+    if (scratch_bytes < qb200_sse_parse_scratch_bytes(n_events) || !scratch) return fail(QB200_ESCRATCH, "sse_parse_batch: scratch too small");
+    set_i64_kernel<<<1, 1, 0, stream>>>(n_host, 0);
+    LAUNCHED("set_i64_kernel");
+    if (n_events == 0) {
+        set_i64_kernel<<<1, 1, 0, stream>>>(out_off, 0);
+        LAUNCHED("set_i64_kernel");
+        CUDA_TRY(cudaGetLastError());
+        return QB200_OK;
+    }
+    uint8_t* sp = (uint8_t*)scratch;
+    const size_t slot = align256((size_t)(n_events + 2) * 8);
+    int64_t* ev_s = (int64_t*)sp;
+    int64_t* ev_e = (int64_t*)(sp + slot);
+    int64_t* cs = (int64_t*)(sp + 2 * slot);
+    int64_t* ce = (int64_t*)(sp + 3 * slot);
+    int64_t* lens = (int64_t*)(sp + 4 * slot);
+    int64_t* partial = (int64_t*)(sp + 5 * slot);
+    if (n_http > 0) {
+        sse_split_write_kernel<<<(unsigned)((n_http + 127) / 128), 128, 0, stream>>>(http_bytes, http_off, n_http, ev_first, ev_s, ev_e);
+        LAUNCHED("sse_split_write_kernel");
+    }
+    const unsigned eg = (unsigned)((n_events + 127) / 128);
+    sse_parse_kernel<<<eg, 128, 0, stream>>>(http_bytes, ev_s, ev_e, n_events, ev_kind, cs, ce, lens, (unsigned long long*)n_host);
+    LAUNCHED("sse_parse_kernel");
+    launch_scan(lens, n_events, out_off, partial, stream);
+    sse_unescape_kernel<<<eg, 128, 0, stream>>>(http_bytes, n_events, ev_kind, cs, ce, out_off, out_bytes);
+    LAUNCHED("sse_unescape_kernel");
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
 }

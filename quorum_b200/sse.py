@@ -10,7 +10,7 @@ from __future__ import annotations
 
 import ctypes
 import json
-from typing import List, Optional, Sequence, Tuple
+from typing import List, Optional, Sequence, Tuple  # noqa: F401
 
 import torch
 
@@ -90,3 +90,57 @@ def frame_final_event(text: str, created: int, device=None) -> bytes:
     data, off = _b.pack_host([_enc(text)])
     out, out_off = frame_events_device(_to_device(data, dev), _to_device(off, dev), None, [prefix], suffix, skip_empty=False)
     return _b.split_host(out, out_off)[0]
+
+
+# ---- SSE input parsing (row f2): HTTP chunks of the backends' streams -> deltas ------------------------------------------
+
+def parse_http_chunks_device(http_bytes: torch.Tensor, http_off: torch.Tensor):
+    """Device buffers in, device buffers out (qb200_sse_split_batch + qb200_sse_parse_batch).
+
+    Returns (out_bytes, out_off, ev_kind, ev_first, n_host): event k of chunk c (k in [ev_first[c], ev_first[c+1])) has
+    kind ev_kind[k] (0 no delta, 1 delta, 2 host decides) and content out_bytes[out_off[k]:out_off[k+1]].  One host
+    synchronisation (the number of events sizes the second call)."""
+    dev = http_off.device
+    n_http = http_off.numel() - 1
+    with torch.cuda.device(dev):
+        ev_first = torch.empty(n_http + 1, dtype=torch.int64, device=dev)
+        scratch = torch.empty(lib().qb200_sse_split_scratch_bytes(n_http), dtype=torch.uint8, device=dev)
+        check(lib().qb200_sse_split_batch(_b._ptr(http_bytes), _b._ptr(http_off), n_http, _b._ptr(ev_first), _b._ptr(scratch),
+                                          scratch.numel(), _b._stream_ptr(dev)))
+        n_events = int(ev_first[-1].item())
+        out = torch.empty(max(int(http_bytes.numel()), 16), dtype=torch.uint8, device=dev)
+        out_off = torch.empty(n_events + 1, dtype=torch.int64, device=dev)
+        kind = torch.empty(max(n_events, 1), dtype=torch.uint8, device=dev)
+        n_host = torch.empty(1, dtype=torch.int64, device=dev)
+        scratch = torch.empty(lib().qb200_sse_parse_scratch_bytes(n_events), dtype=torch.uint8, device=dev)
+        check(lib().qb200_sse_parse_batch(_b._ptr(http_bytes), _b._ptr(http_off), n_http, _b._ptr(ev_first), n_events, _b._ptr(out),
+                                          out.numel(), _b._ptr(out_off), _b._ptr(kind), _b._ptr(n_host), _b._ptr(scratch),
+                                          scratch.numel(), _b._stream_ptr(dev)))
+    return out, out_off, kind[:n_events], ev_first, n_host
+
+
+def parse_http_chunks(chunks: Sequence[bytes], device=None) -> List[Optional[List[str]]]:
+    """parse_sse_chunk (quorum_b200/streaming.py, i.e. oai_proxy.py:578-617) over a batch of HTTP chunks on the device:
+    per chunk the list of deltas in order, or None when the chunk does not decode.  A chunk with an event the device
+    parser is not certain about (kind 2) is parsed by the host function instead, exceptions included."""
+    from .streaming import parse_sse_chunk
+    from .filter import _dec
+    if not chunks:
+        return []
+    dev = _device(device)
+    data, off = _b.pack_host([bytes(c) for c in chunks])
+    d_data = _to_device(data if data.numel() else torch.zeros(16, dtype=torch.uint8), dev)
+    out, out_off, kind, ev_first, n_host = parse_http_chunks_device(d_data, _to_device(off, dev))
+    first = ev_first.cpu().tolist()
+    kinds = kind.cpu().numpy()
+    pieces = _b.split_host(out, out_off)
+    res: List[Optional[List[str]]] = []
+    for c, chunk in enumerate(chunks):
+        a, b = first[c], first[c + 1]
+        if a == b:
+            res.append(None)
+        elif (kinds[a:b] == 2).any():
+            res.append(parse_sse_chunk(bytes(chunk)))
+        else:
+            res.append([_dec(pieces[k]) for k in range(a, b) if kinds[k] == 1])
+    return res

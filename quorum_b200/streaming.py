@@ -4,7 +4,8 @@
 decode, split into events, `data: ` prefix, `[DONE]`, JSON parse, `choices[0].delta.content` — and pushes all deltas
 of the chunk through the GPU filter in one call.  `ConcatenateStreamSession` holds one assembler per backend like
 `tag_filters` (oai_proxy.py:543-545) and produces the final joined text (oai_proxy.py:759-764, 841).
-SSE/JSON framing itself stays on the host (SURVEY.md section 8f marks it as a later row).
+The same parsing runs on the GPU over a batch of chunks in quorum_b200.sse.parse_http_chunks (section 8 row f2), which
+hands any event it is not certain about back to parse_sse_chunk below.
 """
 from __future__ import annotations
 
@@ -46,9 +47,10 @@ def parse_sse_chunk(chunk: bytes) -> Optional[List[str]]:
 class ConcatenateStreamSession:
     """One streaming request over `n_backends` backends (progress_streaming_aggregator, oai_proxy.py:489-885, hot lines only)."""
 
-    def __init__(self, strategy: ConcatenateStrategy, n_backends: int, device=None):
+    def __init__(self, strategy: ConcatenateStrategy, n_backends: int, device=None, device_parse: bool = False):
         self.strategy = strategy
         self.n = n_backends
+        self.device, self.device_parse = device, device_parse  # device_parse: SSE/JSON parsing on the GPU too (quorum_b200.sse)
         self.all_content = ["" for _ in range(n_backends)]          # oai_proxy.py:552
         self._content = ["" for _ in range(n_backends)]
         self._filters = (ThinkingTagFilterBatch(strategy.thinking_tags, n_backends, device)
@@ -57,7 +59,15 @@ class ConcatenateStreamSession:
     def feed_http_chunks(self, chunks: Sequence[Optional[bytes]]) -> List[List[str]]:
         """chunks[i] = the next HTTP chunk of backend i (None = nothing arrived).  Returns, per backend, the filtered
         deltas to re-emit as SSE events (empty strings are not emitted, oai_proxy.py:625-628)."""
-        deltas = [(parse_sse_chunk(c) or []) if c is not None else [] for c in chunks]
+        if self.device_parse:
+            from . import sse
+            present = [i for i, c in enumerate(chunks) if c is not None]
+            parsed = sse.parse_http_chunks([chunks[i] for i in present], self.device)
+            deltas = [[] for _ in chunks]
+            for i, d in zip(present, parsed):
+                deltas[i] = d or []
+        else:
+            deltas = [(parse_sse_chunk(c) or []) if c is not None else [] for c in chunks]
         if self._filters is not None:
             safe = self._filters.feed_chunks(deltas)               # oai_proxy.py:618-621
         else:

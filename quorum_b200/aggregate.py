@@ -22,7 +22,13 @@ DEFAULT_TEMPLATE = ("You have received the following responses regarding the use
                     "Provide a concise synthesis of these responses.")
 
 
-def assemble_prompts_device(resp_bytes: torch.Tensor, resp_off: torch.Tensor, req_off: torch.Tensor, heads: Optional[Sequence[bytes]],
+def pack_heads(heads: Sequence[bytes], dev):
+    """The per-request heads as device buffers (bytes, offsets, total bytes), for assemble_prompts_device."""
+    hb, ho = _b.pack_host(list(heads))
+    return _to_device(hb if hb.numel() else torch.zeros(1, dtype=torch.uint8), dev), _to_device(ho, dev), int(ho[-1])
+
+
+def assemble_prompts_device(resp_bytes: torch.Tensor, resp_off: torch.Tensor, req_off: torch.Tensor, heads,
                             labels: Sequence[bytes], sep: bytes, tail: bytes):
     """Device buffers in, device buffers out: prompt q is out[out_off[q]:out_off[q+1]]."""
     dev = resp_off.device
@@ -33,10 +39,10 @@ def assemble_prompts_device(resp_bytes: torch.Tensor, resp_off: torch.Tensor, re
 
     head_b = head_o = None
     head_total = 0
-    if heads is not None:
-        hb, ho = _b.pack_host(list(heads))
-        head_total = int(ho[-1])
-        head_b, head_o = _to_device(hb if hb.numel() else torch.zeros(1, dtype=torch.uint8), dev), _to_device(ho, dev)
+    if isinstance(heads, tuple):  # already on the device: (bytes, offsets, total) from pack_heads
+        head_b, head_o, head_total = heads
+    elif heads is not None:
+        head_b, head_o, head_total = pack_heads(heads, dev)
     lo = [0]
     for lab in labels:
         lo.append(lo[-1] + len(lab))

@@ -57,22 +57,42 @@ __device__ inline void strip_bounds(const uint8_t* p, int64_t& s, int64_t& e) {
     s += a;
 }
 
-// The events of one HTTP chunk: callback(start, end) for every piece of chunk.decode().strip().split("\n\n"), in order.
-// Returns the number of pieces (>= 1), or 0 when the chunk does not decode (the reference drops it whole, :580-588).
-template <class F>
-__device__ inline int64_t for_each_event(const uint8_t* p, int64_t s, int64_t e, F&& cb) {
-    if (!utf8_valid(p + s, e - s)) return 0;
-    strip_bounds(p, s, e);
-    int64_t count = 0, start = s, i = s;
-    while (i + 1 < e) {
-        if (p[i] == '\n' && p[i + 1] == '\n') {
-            cb(count, start, i);
-            count++;
-            start = i + 2;
-            i += 2;
-        } else {
-            i++;
+// The events of one HTTP chunk: callback(k, start, end) for every piece of chunk.decode().strip().split("\n\n"), in
+// order.  Returns the number of pieces (>= 1), or 0 when the chunk does not decode (the reference drops it whole,
+// :580-588).  One pass over the bytes does both the UTF-8 check (VALIDATE; CPython's strict decoder, see utf8_valid) and
+// the split; the strip only looks at the two ends.
+template <bool VALIDATE, class F>
+__device__ inline int64_t for_each_event(const uint8_t* p, int64_t s0, int64_t e0, F&& cb) {
+    int64_t s = s0, e = e0;
+    strip_bounds(p, s, e);  // on bytes that do not decode this may be off, and the result is discarded below
+    int64_t count = 0, start = s, i = VALIDATE ? s0 : s;
+    const int64_t stop = VALIDATE ? e0 : e;
+    while (i < stop) {
+        const uint8_t c = p[i];
+        if (c < 0x80) {
+            if (c == '\n' && i >= start && i + 1 < e && p[i + 1] == '\n') {  // inside the stripped text: a separator
+                cb(count, start, i);
+                count++;
+                start = i + 2;
+                i += 2;
+            } else {
+                i++;
+            }
+            continue;
         }
+        if (!VALIDATE) {
+            i++;
+            continue;
+        }
+        if (c < 0xC2 || c > 0xF4) return 0;
+        const int need = c < 0xE0 ? 1 : c < 0xF0 ? 2 : 3;
+        if (i + need >= e0) return 0;  // truncated
+        const uint8_t c1 = p[i + 1];
+        if ((c1 & 0xC0) != 0x80) return 0;
+        if ((c == 0xE0 && c1 < 0xA0) || (c == 0xED && c1 >= 0xA0) || (c == 0xF0 && c1 < 0x90) || (c == 0xF4 && c1 >= 0x90)) return 0;
+        for (int k = 2; k <= need; k++)
+            if ((p[i + k] & 0xC0) != 0x80) return 0;
+        i += need + 1;
     }
     cb(count, start, e);
     return count + 1;
@@ -82,7 +102,7 @@ __global__ void sse_split_count_kernel(const uint8_t* __restrict__ http, const i
                                        int64_t* __restrict__ counts) {
     const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= n_http) return;
-    counts[c] = for_each_event(http, off[c], off[c + 1], [](int64_t, int64_t, int64_t) {});
+    counts[c] = for_each_event<true>(http, off[c], off[c + 1], [](int64_t, int64_t, int64_t) {});
 }
 
 __global__ void sse_split_write_kernel(const uint8_t* __restrict__ http, const int64_t* __restrict__ off, int64_t n_http,
@@ -90,7 +110,8 @@ __global__ void sse_split_write_kernel(const uint8_t* __restrict__ http, const i
     const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= n_http) return;
     const int64_t base = ev_first[c];
-    for_each_event(http, off[c], off[c + 1], [&](int64_t k, int64_t a, int64_t b) {
+    if (ev_first[c + 1] == base) return;  // did not decode: no events
+    for_each_event<false>(http, off[c], off[c + 1], [&](int64_t k, int64_t a, int64_t b) {
         ev_s[base + k] = a;
         ev_e[base + k] = b;
     });

@@ -144,3 +144,78 @@ def parse_http_chunks(chunks: Sequence[bytes], device=None) -> List[Optional[Lis
         else:
             res.append([_dec(pieces[k]) for k in range(a, b) if kinds[k] == 1])
     return res
+
+
+# ---- the whole streaming step on the device: HTTP chunks in, SSE events out ---------------------------------------------
+
+class DeviceStreamPipeline:
+    """What progress_streaming_aggregator does per HTTP chunk of every backend (oai_proxy.py:578-652), batched over
+    `n_streams` streams with the data staying on the device between the three steps: parse the chunks (row f2), feed the
+    deltas through the ThinkingTagFilter of their stream with carried state (a3), frame every non-empty filtered delta
+    as the reference's SSE event (f1).  `backend_of_stream[s]` is the i of `chatcmpl-parallel-{i}` for stream s."""
+
+    def __init__(self, thinking_tags: Sequence[str], backend_of_stream: Sequence[int], created: int, device=None,
+                 hide_intermediate_think: bool = True):
+        self.dev = _device(device)
+        self.n = len(backend_of_stream)
+        self.table = _b.tag_table(list(thinking_tags))
+        self.hide = hide_intermediate_think
+        self.state = _b.new_stream_state(self.n, self.dev)
+        ids = sorted(set(int(i) for i in backend_of_stream))
+        slot = {i: k for k, i in enumerate(ids)}
+        env = [event_envelope(backend_event_id(i), created) for i in ids]
+        self.prefixes, self.suffix = [e[0] for e in env], env[0][1]
+        self.slot_of_stream = torch.tensor([slot[int(i)] for i in backend_of_stream], dtype=torch.int32).to(self.dev)
+        self.content = [[] for _ in range(self.n)]  # filtered bytes per stream, for the final join (oai_proxy.py:624)
+
+    def step(self, chunks: Sequence[Optional[bytes]]) -> List[List[bytes]]:
+        """chunks[s] = the HTTP chunk that arrived for stream s (None: nothing).  Returns, per stream, the SSE events to
+        send on, in order."""
+        from .streaming import parse_sse_chunk
+        if len(chunks) != self.n:
+            raise ValueError("one entry per stream")
+        dev = self.dev
+        data, off = _b.pack_host([bytes(c) if c is not None else b"" for c in chunks])
+        d_data = _to_device(data if data.numel() else torch.zeros(16, dtype=torch.uint8), dev)
+        out, out_off, kind, ev_first, n_host = parse_http_chunks_device(d_data, _to_device(off, dev))
+        if int(n_host.item()):  # an event the device is not certain about: those chunks go through the reference's code path
+            first, kinds = ev_first.cpu().tolist(), kind.cpu().numpy()
+            pieces = _b.split_host(out, out_off)
+            deltas = []
+            for s, c in enumerate(chunks):
+                a, b = first[s], first[s + 1]
+                if c is not None and (kinds[a:b] == 2).any():
+                    deltas.append([_enc(t) for t in (parse_sse_chunk(bytes(c)) or [])])
+                else:
+                    deltas.append([pieces[k] for k in range(a, b) if kinds[k] == 1])
+            flat = [d for ds in deltas for d in ds]
+            hb, ho = _b.pack_host(flat)
+            out, out_off = _to_device(hb if hb.numel() else torch.zeros(16, dtype=torch.uint8), dev), _to_device(ho, dev)
+            so = [0]
+            for ds in deltas:
+                so.append(so[-1] + len(ds))
+            ev_first = torch.tensor(so, dtype=torch.int64).to(dev)
+        n_events = out_off.numel() - 1
+        if self.hide:
+            f_bytes, f_off, self.state = _b.stream_feed_batch(self.table, out, out_off, ev_first, self.state, state_out=self.state)
+        else:
+            f_bytes, f_off = out, out_off
+        # the stream of every event: events are grouped by stream in order
+        counts = ev_first[1:] - ev_first[:-1]
+        ev_slot = torch.repeat_interleave(self.slot_of_stream, counts, output_size=n_events)
+        framed, framed_off = frame_events_device(f_bytes, f_off, ev_slot, self.prefixes, self.suffix, skip_empty=True)
+        first = ev_first.cpu().tolist()
+        events = _b.split_host(framed, framed_off)
+        texts = _b.split_host(f_bytes, f_off)
+        res: List[List[bytes]] = []
+        for s in range(self.n):
+            a, b = first[s], first[s + 1]
+            self.content[s].extend(texts[a:b])
+            res.append([e for e in events[a:b] if e])
+        return res
+
+    def finish(self) -> List[str]:
+        """flush() every filter (oai_proxy.py:739-741: returns "", drops a held partial) and return each stream's content."""
+        from .filter import _dec
+        _b.stream_flush_batch(self.state)
+        return [_dec(b"".join(c)) for c in self.content]

@@ -193,3 +193,57 @@ def test_gpu_parser_mutation_fuzz():
             with pytest.raises(Exception) as ei:
                 qb.sse.parse_http_chunks([c])
             assert type(ei.value).__name__ == e[1], c
+
+
+@pytest.mark.gpu
+def test_device_stream_pipeline_matches_the_reference_loop():
+    """HTTP chunks in, SSE events out, three device steps in a row: against the reference's per-chunk loop replayed with its
+    own pieces (parse_sse_chunk = :578-617, the oracle filter = :278-350, json.dumps framing = :629-652)."""
+    import quorum_b200 as qb
+    from oracle import quorum_oracle as o
+    from quorum_b200.streaming import parse_sse_chunk
+    rng = random.Random(13)
+    tags = ["think", "reason", "reasoning", "thought"]
+    n, created = 40, 1712000000
+    backend = [s % 3 for s in range(n)]
+    pieces = ["Hello ", "<thi", "nk>", "secret", "</th", "ink>", " world", "é日本", "<", "reason>", "</reason>", "\n", '"q"', "\\", "x<y "]
+    # per stream a sequence of deltas, cut into HTTP chunks of 0-3 events, some with comments / [DONE] / broken JSON
+    streams = []
+    for s in range(n):
+        deltas = [rng.choice(pieces) for _ in range(rng.randrange(5, 40))]
+        chunks, k = [], 0
+        while k < len(deltas):
+            m = rng.randrange(0, 4)
+            evs = ["data: " + json.dumps({"choices": [{"index": 0, "delta": {"content": t}}]}, ensure_ascii=rng.random() < 0.5)
+                   for t in deltas[k:k + m]]
+            if rng.random() < 0.1:
+                evs.append(": ping")
+            if rng.random() < 0.05:
+                evs.append("data: {\"choices\": [{\"delta\": {\"content\": \"broken")
+            if rng.random() < 0.05:
+                evs.append("data: {\"choices\": [{\"delta\": {\"content\": \"dup\", \"content\": \"last wins\"}}]}")
+            chunks.append(("\n\n".join(evs) + "\n\n").encode())
+            k += m
+        chunks.append(b"data: [DONE]\n\n")
+        streams.append(chunks)
+    pipe = qb.sse.DeviceStreamPipeline(tags, backend, created)
+    filters = [o.ThinkingTagFilter(tags) for _ in range(n)]
+    content = ["" for _ in range(n)]
+    for step in range(max(len(c) for c in streams)):
+        batch_chunks = [c[step] if step < len(c) and rng.random() < 0.9 else None for c in streams]
+        for s, c in enumerate(batch_chunks):  # a chunk that was withheld this step comes in the next one
+            if c is None and step < len(streams[s]):
+                streams[s].insert(step, None)
+        got = pipe.step(batch_chunks)
+        for s, c in enumerate(batch_chunks):
+            exp = []
+            if c is not None:
+                for delta in parse_sse_chunk(c) or []:
+                    safe = filters[s].feed(delta)
+                    content[s] += safe
+                    if safe:
+                        ev = {"id": f"chatcmpl-parallel-{backend[s]}", "object": "chat.completion.chunk", "created": created,
+                              "model": "parallel-proxy", "choices": [{"index": 0, "delta": {"content": safe}, "finish_reason": None}]}
+                        exp.append(f"data: {json.dumps(ev)}\n\n".encode())
+            assert got[s] == exp, (step, s, c)
+    assert pipe.finish() == content

@@ -220,3 +220,40 @@ def test_chained_slices_and_pipelined_host_strip_concat(qb):
             torch.cuda.synchronize()
             assert np.array_equal(sess.h_oo[: len(exp_off)].numpy(), exp_off), (streaming, slices)
             assert np.array_equal(sess.h_out[: int(exp_off[-1])].numpy(), exp_out), (streaming, slices)
+
+
+@pytest.mark.parametrize("cfg", ["cfg3", "cfg4"])
+def test_cfg3_cfg4_full_size_sampled_against_oracle(qb, cfg):
+    """BASELINE.json configs[2] (1M responses x 4 KiB, 4 per request, multi-byte separator) and configs[3] (8 x 32 KiB
+    per request, 70 % inside <think>) at full size: every request's length is checked against the oracle's per-response
+    kept lengths (a request is a sum over its responses + separators), 300 random requests byte for byte."""
+    from oracle import c_oracle
+    from quorum_b200 import synth
+    dev = torch.device("cuda", 0)
+    if cfg == "cfg3":
+        base, n_resp, per_req, sep = synth.cfg3_base(4096), 1_000_000, 4, synth.SEP_MULTIBYTE.encode()
+    else:
+        base, n_resp, per_req, sep = synth.cfg4_base(512), 131_072, 8, b"\n-------------\n"
+    ub = base.shape[1]
+    idx = synth.gather_units(base, n_resp, seed=1000)
+    idx_t = torch.from_numpy(idx).to(dev)
+    data = torch.from_numpy(base).to(dev).index_select(0, idx_t).reshape(-1).contiguous()
+    in_off = torch.arange(0, n_resp * ub + 1, ub, dtype=torch.int64, device=dev)
+    req_off = torch.arange(0, n_resp + 1, per_req, dtype=torch.int64, device=dev)
+    sep_t = torch.frombuffer(bytearray(sep), dtype=torch.uint8).to(dev)
+    out, out_off, rlen = qb.batch.strip_concat_batch(qb.batch.tag_table(synth.TAGS5), data, in_off, req_off, sep_t, hide=True,
+                                                     streaming=False, want_resp_len=True)
+    torch.cuda.synchronize()
+    # oracle over the base pool: kept length and bytes of every distinct response
+    flat = np.ascontiguousarray(base).reshape(-1)
+    bo = np.arange(0, flat.size + 1, ub, dtype=np.int64)
+    e_out, e_off, e_len = c_oracle.strip_concat_batch(c_oracle.Tags(synth.TAGS5), flat, bo, None, b"", c_oracle.FLAG_HIDE)
+    assert np.array_equal(rlen[:n_resp].cpu().numpy(), e_len[idx])           # every response's filtered length
+    n_req = n_resp // per_req
+    exp_req = e_len[idx].reshape(n_req, per_req).sum(1) + (per_req - 1) * len(sep)
+    got_off = out_off.cpu().numpy()
+    assert got_off[0] == 0 and np.array_equal(np.diff(got_off), exp_req)      # offsets: prefix sum of the request lengths
+    rng = np.random.default_rng(12)
+    for q in rng.integers(0, n_req, 300):
+        parts = [bytes(e_out[e_off[b]:e_off[b + 1]]) for b in idx[q * per_req:(q + 1) * per_req]]
+        assert bytes(out[got_off[q]:got_off[q + 1]].cpu().numpy()) == sep.join(parts)

@@ -850,7 +850,11 @@ size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req, int64_t o
 
 static int grid_for(int64_t units) {
     int64_t g = (units + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    const int64_t cap = 148 * 64;  // grid-stride beyond this
+    int64_t cap = 148 * 64;  // grid-stride beyond this
+    if (const char* e = getenv("QB200_GRID_CAP")) {  // test knob: a small grid makes every block loop (and take many tickets)
+        const int64_t v = atoll(e);
+        if (v > 0) cap = v;
+    }
     if (g > cap) g = cap;
     if (g < 1) g = 1;
     return (int)g;

@@ -257,3 +257,32 @@ def test_cfg3_cfg4_full_size_sampled_against_oracle(qb, cfg):
     for q in rng.integers(0, n_req, 300):
         parts = [bytes(e_out[e_off[b]:e_off[b + 1]]) for b in idx[q * per_req:(q + 1) * per_req]]
         assert bytes(out[got_off[q]:got_off[q + 1]].cpu().numpy()) == sep.join(parts)
+
+
+def test_small_grid_blocks_loop_and_take_many_tickets(qb, monkeypatch):
+    """QB200_GRID_CAP=3: every warp-per-unit / lane-per-unit kernel runs with three blocks, so blocks loop over many groups
+    and the count kernel's look-back sees blocks that each took dozens of tickets.  Same bytes as the oracle."""
+    from oracle import c_oracle
+    from quorum_b200 import synth
+    monkeypatch.setenv("QB200_GRID_CAP", "3")
+    dev = torch.device("cuda", 0)
+    base = synth.cfg2_base(64)
+    n = 20000
+    idx = synth.gather_units(base, n, seed=3)
+    data = np.ascontiguousarray(base[idx]).reshape(-1)
+    chunk_off = np.arange(0, data.size + 1, 64, dtype=np.int64)
+    stream_off = np.arange(0, n * 256 + 1, 256, dtype=np.int64)
+    exp_out, exp_oco, exp_st = c_oracle.stream_feed_batch(c_oracle.Tags(synth.TAGS5), data, chunk_off, stream_off, None, 0)
+    out, oco, st = qb.batch.stream_feed_batch(qb.batch.tag_table(synth.TAGS5), _t(data, dev), _t(chunk_off, dev), _t(stream_off, dev),
+                                              None, flush=False)
+    torch.cuda.synchronize()
+    assert np.array_equal(oco.cpu().numpy(), exp_oco)
+    assert np.array_equal(out[: int(exp_oco[-1])].cpu().numpy(), exp_out)
+    units = synth.cfg5_units(4 << 20, seed=41)
+    d2, in_off = synth.pack(units)
+    req = np.arange(0, len(units) + 1, 1, dtype=np.int64)
+    e_out, e_off, _ = c_oracle.strip_concat_batch(c_oracle.Tags(synth.TAGS5), d2, in_off, req, b"", c_oracle.FLAG_HIDE)
+    o2, off2, _ = qb.batch.strip_concat_batch(qb.batch.tag_table(synth.TAGS5), _t(d2, dev), _t(in_off, dev), _t(req, dev), None, hide=True,
+                                              streaming=False)
+    torch.cuda.synchronize()
+    assert np.array_equal(off2.cpu().numpy(), e_off) and np.array_equal(o2[: int(e_off[-1])].cpu().numpy(), e_out)

@@ -558,17 +558,16 @@ struct StreamWalker {
 };
 
 // ------------------------------------------------------------------------------------------------------------------
-// Record-driven stream walker ("run list"): the fast path of ThinkingTagFilter.feed.
+// Record-driven stream walker, one warp per stream (the count kernel uses it for streams too long for one lane, see
+// qb_lane.cuh for the lane-per-stream version of the same walk).
 //
 // Same semantics as StreamWalker, different shape of work: nothing here loops over the text.
-//   1  the warp walks the unit's token records (only steps that have any) and collects the kept runs of the unit,
-//      one run per lane (more than 32 runs, or a step whose records overflowed: `overflow`, the caller falls back to
-//      StreamWalker); the source lines of the runs are prefetched right away;
-//   2  the feed boundaries are handled 32 at a time, one per lane: released bytes before c = carried literal bytes +
-//      overlap of [0, c) with the runs; the hold-back test looks up the last '<' before c in the step's records;
-//   3  the runs are copied to their final place with 16-byte stores; carried state is written.
-// The count pass is phase 1 plus the last boundary.  Positions are unit-relative int32 (units of 2 GiB and more take
-// the fallback).
+//   1  the warp walks the unit's token records (only steps that have any): the kept runs of the unit, one run per lane,
+//      and the hold intervals of the '<' that stay text at depth 0 (more than the descriptor holds, or a step whose
+//      records overflowed: `overflow`, the caller falls back to StreamWalker);
+//   2  the last feed boundary (c = n) decides the released total and what is carried;
+//   3  descriptor (for the offsets and finish kernels) and carried state are written.
+// Positions are unit-relative int32 (units of 2 GiB and more take the fallback).
 // ------------------------------------------------------------------------------------------------------------------
 // The largest e in [c, min(x + kHeldMax, n)] such that text[x, e) is a proper prefix of an open tag (hold-back test,
 // oai_proxy.py:311-323), or c - 1 when text[x, c) is none.  The test is monotone in e.  Out of line: rare.
@@ -886,7 +885,7 @@ struct StripRunWalker {
     bool wide = false;
     int64_t kept_len = 0;
     uint8_t* dst = nullptr;
-    UnitDesc* desc = nullptr;  // count pass: where the trimmed runs go (copied later by the gather kernel)
+    UnitDesc* desc = nullptr;  // count pass: where the trimmed runs go (copied later by strip_copy_kernel)
 
     __device__ StripRunWalker(const DevTags& tg_, const uint8_t* buf_, int64_t total_, int64_t ustart_, int64_t n_,
                               unsigned long long* lc, int lane_, TokSrc ts_)

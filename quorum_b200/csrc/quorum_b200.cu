@@ -1,10 +1,13 @@
 // quorum_b200 — kernels + C ABI (include/quorum_b200.h).  sm_100a only; no CPU fallback.
 //
-// General path ("warp per unit"): works for any unit size straight from global memory.
-//   strip_concat:  count kernel (filter + strip lengths)  ->  layout kernels (per-request prefix sums incl. separators)
-//                  ->  copy kernel (re-walk, vectorised copy to the final offsets)
-//   stream_feed :  count kernel (released bytes per stream) -> scan over streams -> copy kernel (bytes, per-chunk offsets,
-//                  carried state)
+// Default path (QB200_PATH=token), see DESIGN.md section 5.1:
+//   stream_feed :  tokenize (one record per '<')  ->  count (lane per stream: automaton over the records, descriptor,
+//                  carried state, prefix sum over the streams by look-back)  ->  offsets (thread per feed boundary)
+//                  ->  finish (warp per stream: kept runs to their final place)
+//   strip_concat:  tokenize  ->  count (lane per response: liveness, automaton, strip(), descriptor)  ->  request layout,
+//                  scan, finalize (per-request prefix sums incl. separators)  ->  copy (warp per response)
+// QB200_PATH=general: the byte-rescanning warp-per-unit walkers (count, scan, copy); QB200_PATH=tile: qb_tile.cuh.
+// Then the rows around the filter: SSE framing (qb_sse.cuh), SSE parsing (qb_ssein.cuh), aggregate prompts (qb_agg.cuh).
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>

@@ -105,7 +105,8 @@ int qb200_strip_concat_batch(const qb200_tags *tags, const uint8_t *in_bytes, co
  * arrays stay those of the WHOLE batch, `stream_off` points at the slice's first stream (its entries are still absolute
  * chunk indices), `n_streams` is the slice's stream count, state pointers point at the slice's first stream, and the
  * slice's output starts at out_chunk_off[stream_off[0]], which the previous slice's call wrote (the first slice is called
- * without the flag).  Slices must be issued in order on one stream; only the slice's bytes need to be resident. */
+ * without the flag).  Slices must be issued in order on one stream; only the slice's bytes and chunk offsets need to be
+ * resident, plus chunk_off[n_chunks] (the total, which bounds every read). */
 size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity);
 int qb200_stream_feed_batch(const qb200_tags *tags, const uint8_t *chunk_bytes, const int64_t *chunk_off,
                             int64_t n_chunks, const int64_t *stream_off, int64_t n_streams,

@@ -266,6 +266,7 @@ class HostStreamFeeder:
         d_data, d_co, d_so, d_oco = self.d_data[:nb], self.d_co[:nc + 1], self.d_so[:ns + 1], self.d_oco[:nc + 1]
         with torch.cuda.stream(s_in):
             d_so.copy_(h_stream_off, non_blocking=True)
+            d_co[nc:nc + 1].copy_(h_chunk_off[nc:nc + 1], non_blocking=True)     # the kernels bound their reads by chunk_off[n_chunks]
         sb = [ns * k // slices for k in range(slices + 1)]                      # stream bounds
         cb = [int(h_stream_off[i]) for i in sb]                                # chunk bounds (host reads, pinned)
         bb = [int(h_chunk_off[c]) for c in cb]                                 # byte bounds

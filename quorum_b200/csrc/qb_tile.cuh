@@ -288,7 +288,8 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
     TileShared& S = *reinterpret_cast<TileShared*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const DevTags& tg = P.tg;
-    const int64_t total = P.chunk_off[P.n_chunks];
+    // the call's streams end at chunk stream_off[n_streams] (a first slice of a chained batch stops short of n_chunks)
+    const int64_t total = P.chunk_off[P.stream_off[P.n_streams]];
     const int64_t n_tiles = total / kWindow + 1 <= P.max_tiles ? total / kWindow + 1 : P.max_tiles;
     uint32_t parity = 0;
     if (tid == 0) mbar_init(&S.mbar, 1);
@@ -372,7 +373,7 @@ __global__ void __launch_bounds__(kTileThreads, 4) stream_tile_kernel(const __gr
         if (fast) {
             for (int u = tid; u <= nunits; u += kTileThreads) {
                 const int64_t s = S.u0 + u;
-                const int64_t cs = s < P.n_streams ? P.stream_off[s] : P.n_chunks;
+                const int64_t cs = P.stream_off[s < P.n_streams ? s : P.n_streams];
                 const int64_t b = P.chunk_off[cs];
                 if (u < nunits) {
                     S.u_beg[u] = (int32_t)(b - g0);

@@ -172,9 +172,11 @@ def test_cfg2_full_size_sampled_against_oracle(qb):
     assert np.array_equal(depth, e_st["depth"][idx])
 
 
-def test_chained_slices_and_pipelined_host_feeder(qb):
+@pytest.mark.parametrize("path", ["token", "tile", "general"])
+def test_chained_slices_and_pipelined_host_feeder(qb, path_env, path):
     """QB200_CHAIN: a batch fed slice by slice (what the host-buffer session does to overlap PCIe copies with compute)
-    gives the same bytes and the same per-chunk offsets as one call."""
+    gives the same bytes and the same per-chunk offsets as one call, whichever implementation takes the first slice."""
+    os.environ["QB200_PATH"] = path
     from oracle import c_oracle
     from quorum_b200 import synth
     dev = torch.device("cuda", 0)

@@ -133,15 +133,24 @@ __device__ __forceinline__ bool stream_walk_lane(const DevTags& tg, const uint8_
 #pragma unroll
           for (int i = 0; i < 8; i++)
               if ((cpack >> (8 * i)) & 0xFF) asm volatile("prefetch.global.L1 [%0];" ::"l"(ts.rec + (s0 + i) * kRecPerStep));
-          for (int i = 0; i < 8; i++) {
-            const int cnt = (int)((cpack >> (8 * i)) & 0xFF);
-            if (cnt == 0) continue;
-            if (cnt == kRecOverflow) return false;
-            const int64_t sj = s0 + i;
-            const uint32_t* rp = ts.rec + sj * kRecPerStep;
-            const int sb = (int)((sj << 10) - ustart);  // unit position of the step's first byte
-            for (int q = 0; q < cnt; q++) {
-                const uint32_t r = rp[q];
+          // One loop over this lane's records of the eight steps, whatever step each is in: the lanes of a warp then
+          // iterate max-over-lanes(records) times, not sum-over-steps(max-over-lanes(records in the step)).
+          unsigned long long rest = cpack;
+          const uint32_t* rp = nullptr;
+          int cnt = 0, q = 0, sb = 0;
+          for (;;) {
+                if (q == cnt) {  // next step of the eight that has records
+                    if (rest == 0) break;
+                    const int i = (__ffsll((long long)rest) - 1) >> 3;
+                    cnt = (int)((rest >> (8 * i)) & 0xFF);
+                    rest &= ~(0xFFull << (8 * i));
+                    if (cnt == kRecOverflow) return false;
+                    const int64_t sj = s0 + i;
+                    rp = ts.rec + sj * kRecPerStep;
+                    sb = (int)((sj << 10) - ustart);  // unit position of the step's first byte
+                    q = 0;
+                }
+                const uint32_t r = rp[q++];
                 const int kind = (r >> 17) & 3;
                 const int x = sb + (int)(r & 1023);
                 const int tend = x + (int)((r >> 10) & 127);
@@ -158,7 +167,6 @@ __device__ __forceinline__ bool stream_walk_lane(const DevTags& tg, const uint8_
                     took = on_tag(x, tend, kind == 1, ex);
                 }
                 if (!took && depth == 0) hold_candidate(T, x);
-            }
           }
         }
     }

@@ -11,12 +11,12 @@ from .concatenate import ConcatenateStrategy, concatenate, concatenate_many  # n
 from .filter import (ThinkingTagFilter, ThinkingTagFilterBatch, strip_thinking_tags,  # noqa: F401
                      strip_thinking_tags_many)
 from .install import install, uninstall  # noqa: F401
-from .streaming import ConcatenateStreamSession, parse_sse_chunk  # noqa: F401
+from .streaming import ConcatenateStreamSession, parse_sse_chunk, parse_sse_events  # noqa: F401
 from . import aggregate, batch, sharding, sse  # noqa: F401
 from .aggregate import AggregatePromptBuilder  # noqa: F401
 
 __all__ = [
     "strip_thinking_tags", "strip_thinking_tags_many", "ThinkingTagFilter", "ThinkingTagFilterBatch",
-    "ConcatenateStrategy", "concatenate", "concatenate_many", "ConcatenateStreamSession", "parse_sse_chunk",
+    "ConcatenateStrategy", "concatenate", "concatenate_many", "ConcatenateStreamSession", "parse_sse_chunk", "parse_sse_events",
     "install", "uninstall", "batch", "sharding", "sse", "aggregate", "AggregatePromptBuilder", "QuorumB200Error", "launch_count",
 ]

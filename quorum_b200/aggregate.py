@@ -1,7 +1,7 @@
 """Aggregate-strategy prompt assembly and usage sums on the GPU.
 
 Mirrors what the reference does between the backends' answers and the aggregator call: filter every answer
-(`strip_thinking_tags(content, thinking_tags, hide_intermediate_think)`, src/quorum/oai_proxy.py:1193-1199), then build
+(`strip_thinking_tags(content, thinking_tags, hide_intermediate=hide_final_think)`, src/quorum/oai_proxy.py:1193-1199), then build
     query_format.format(query=user_query) + prompt_template.replace("{responses}", separator.join(label_i + answer_i))
 (:406-423, configuration keys and defaults :1204-1268).  The per-request constants (formatted query, template text around
 the placeholder, labels) are rendered on the host with the same str methods; the filtering, the lengths, the prefix sum
@@ -72,7 +72,10 @@ def usage_sums_device(usage: torch.Tensor, req_off: torch.Tensor) -> torch.Tenso
 
 @dataclass
 class AggregatePromptBuilder:
-    """Same configuration keys and defaults as the reference's aggregate strategy (oai_proxy.py:1204-1268)."""
+    """Same configuration keys and defaults as the reference's aggregate strategy (oai_proxy.py:1204-1268).  The answers
+    are filtered before they reach the prompt exactly as the reference does it (oai_proxy.py:1166-1199): with
+    strip_thinking_tags(content, thinking_tags, hide_intermediate=hide_final_think), both keys read from the block of the
+    strategy named by iterations.aggregation.strategy, hide_final_think defaulting to False."""
     separator: str = "\n\n---\n\n"
     include_original_query: bool = True
     query_format: str = "Original query: {query}\n\n"
@@ -80,7 +83,7 @@ class AggregatePromptBuilder:
     source_label_format: str = "Response from {backend_name}:\n"
     prompt_template: str = DEFAULT_TEMPLATE
     thinking_tags: List[str] = field(default_factory=lambda: ["think", "reason", "reasoning", "thought"])
-    hide_intermediate_think: bool = True
+    hide_final_think: bool = False
     device: Any = None
 
     @classmethod
@@ -89,7 +92,8 @@ class AggregatePromptBuilder:
         tmpl = agg.get("prompt_template", DEFAULT_TEMPLATE)
         if "{intermediate_results}" in tmpl:  # :1244-1247
             tmpl = tmpl.replace("{intermediate_results}", "{responses}")
-        it = config.get("iterations", {}).get("aggregation", {})
+        name = config.get("iterations", {}).get("aggregation", {}).get("strategy", "concatenate")   # :1166-1173
+        it = config.get("strategy", {}).get(name, {})
         return cls(separator=agg.get("intermediate_separator", "\n\n---\n\n"),
                    include_original_query=agg.get("include_original_query", True),
                    query_format=agg.get("query_format", "Original query: {query}\n\n"),
@@ -97,7 +101,7 @@ class AggregatePromptBuilder:
                    source_label_format=agg.get("source_label_format", "Response from {backend_name}:\n"),
                    prompt_template=tmpl,
                    thinking_tags=it.get("thinking_tags", ["think", "reason", "reasoning", "thought"]),
-                   hide_intermediate_think=it.get("hide_intermediate_think", True), device=device)
+                   hide_final_think=it.get("hide_final_think", False), device=device)
 
     def build_prompts(self, contents_per_request: Sequence[Sequence[str]], user_queries: Sequence[str]) -> List[str]:
         """One aggregator prompt per request.  contents_per_request[q] are the backends' raw answers of request q."""
@@ -119,7 +123,7 @@ class AggregatePromptBuilder:
         data, off = _b.pack_host([_enc(c) for c in flat])
         d_data, d_off = _to_device(data if data.numel() else torch.zeros(16, dtype=torch.uint8), dev), _to_device(off, dev)
         table = _b.tag_table(self.thinking_tags)
-        f_bytes, f_off, _ = _b.strip_concat_batch(table, d_data, d_off, None, None, hide=self.hide_intermediate_think, streaming=False)
+        f_bytes, f_off, _ = _b.strip_concat_batch(table, d_data, d_off, None, None, hide=self.hide_final_think, streaming=False)
         ro = [0]
         for cs in contents_per_request:
             ro.append(ro[-1] + len(cs))

@@ -64,12 +64,16 @@ class ConcatenateStrategy:
     suppress_individual_responses: bool = False
 
     @classmethod
-    def from_config(cls, config: dict, strategy_name: Optional[str] = None) -> "ConcatenateStrategy":
+    def from_config(cls, config: dict, strategy_name: Optional[str] = None,
+                    request_body: Optional[dict] = None) -> "ConcatenateStrategy":
         """Reads config["strategy"][name] like oai_proxy.py:1049-1071 (name defaults to
-        config["iterations"]["aggregation"]["strategy"], itself defaulting to "concatenate")."""
+        config["iterations"]["aggregation"]["strategy"], itself defaulting to "concatenate").  `request_body` is the
+        parsed request: its "suppress_individual_responses" key, when present, overrides the config (oai_proxy.py:1072-1075)."""
         if strategy_name is None:
             strategy_name = config.get("iterations", {}).get("aggregation", {}).get("strategy", "concatenate")
         c = config.get("strategy", {}).get(strategy_name, {})
+        if request_body is not None and "suppress_individual_responses" in request_body:
+            c = dict(c, suppress_individual_responses=request_body.get("suppress_individual_responses"))
         return cls(
             separator=c.get("separator", "\n"),
             hide_intermediate_think=c.get("hide_intermediate_think", True),

@@ -35,12 +35,96 @@ __device__ __forceinline__ int tag_at(const DevTags& tg, const uint8_t* buf, int
 
 __device__ __forceinline__ uint32_t lt_any16(const uint4& v) { return lt_any(v.x) | lt_any(v.y) | lt_any(v.z) | lt_any(v.w); }
 
+// One 2 KiB pair of steps `pr` of the flat buffer, by one warp: lane j loads bytes [64j, 64j+64) with four 16-byte loads
+// (lanes 0-15 read the first step, lanes 16-31 the second), so one ballot and one divergent "look at the candidates"
+// branch serve two steps, and each lane has 64 bytes in flight.  cnt / rec are indexed by absolute step (the caller may
+// pass pointers shifted so that the steps of a tile land in shared memory); steps >= nsteps are not written, bytes at and
+// beyond `total` are never read.
+__device__ __forceinline__ void tokenize_pair(const DevTags& tg, const uint8_t* __restrict__ bytes, int64_t total, int64_t nsteps,
+                                              int64_t pr, int lane, uint8_t* cnt, uint32_t* rec) {
+    const int half = lane >> 4;
+    const unsigned hm = half ? 0xFFFF0000u : 0x0000FFFFu;  // the lanes of this lane's step
+    const int64_t a = (pr << 11) + lane * 64;
+    uint32_t lt0 = 0, lt1 = 0;  // '<' positions in bytes [0, 32) and [32, 64) of the lane
+    if (a + 64 <= total) {
+        const uint4* p = reinterpret_cast<const uint4*>(bytes + a);
+        // plain loads, not ld.cs: the candidates' tag match re-reads these lines from L1 (measured: cfg2 0.549 -> 0.541 ms,
+        // cfg3 2.32 -> 2.27, cfg4 1.31 -> 1.29)
+        const uint4 v0 = p[0], v1 = p[1], v2 = p[2], v3 = p[3];
+        const uint32_t f0 = lt_any16(v0), f1 = lt_any16(v1), f2 = lt_any16(v2), f3 = lt_any16(v3);
+        if (f0 | f1 | f2 | f3) {  // exact positions only where needed
+            if (f0) lt0 = lt_mask16(v0);
+            if (f1) lt0 |= lt_mask16(v1) << 16;
+            if (f2) lt1 = lt_mask16(v2);
+            if (f3) lt1 |= lt_mask16(v3) << 16;
+        }
+    } else {
+        for (int b = 0; b < 32 && a + b < total; b++)
+            if (bytes[a + b] == '<') lt0 |= 1u << b;
+        for (int b = 0; b < 32 && a + 32 + b < total; b++)
+            if (bytes[a + 32 + b] == '<') lt1 |= 1u << b;
+    }
+    const unsigned any = __ballot_sync(kFull, (lt0 | lt1) != 0);
+    const int64_t step = (pr << 1) + half;
+    if (any == 0) {  // the common case: no '<' in these 2 KiB
+        if ((lane & 15) == 0 && step < nsteps) cnt[step] = 0;
+        return;
+    }
+    // records of this lane's 64 bytes (more than 8 '<' in them is an overflow)
+    uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0, r5 = 0, r6 = 0, r7 = 0;
+    int nr = 0;
+    bool many = false;
+    unsigned long long lt = (unsigned long long)lt0 | ((unsigned long long)lt1 << 32);
+    while (lt) {
+        const int b = __ffsll((long long)lt) - 1;
+        lt &= lt - 1;
+        int is_close, cls, exotic;
+        const int len = tag_at(tg, bytes, total, a + b, is_close, cls, exotic);
+        const uint32_t r = (uint32_t)((lane & 15) * 64 + b) | ((uint32_t)len << 10) | ((len ? (uint32_t)is_close : 2u) << 17) |
+                           ((uint32_t)cls << 19) | ((uint32_t)exotic << 26);
+        if (nr == 0) r0 = r;
+        else if (nr == 1) r1 = r;
+        else if (nr == 2) r2 = r;
+        else if (nr == 3) r3 = r;
+        else if (nr == 4) r4 = r;
+        else if (nr == 5) r5 = r;
+        else if (nr == 6) r6 = r;
+        else if (nr == 7) r7 = r;
+        else many = true;
+        nr++;
+    }
+    int incl, tot;  // rank of this lane's last record inside its step, records in the step
+    if (__all_sync(kFull, nr <= 1)) {  // one record per lane at most: ranks straight from the ballot
+        incl = __popc(any & hm & (0xffffffffu >> (31 - lane)));
+        tot = __popc(any & hm);
+    } else {
+        incl = nr;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int t = __shfl_up_sync(kFull, incl, d);
+            if (lane >= d) incl += t;
+        }
+        const int t16 = __shfl_sync(kFull, incl, 15), t32 = __shfl_sync(kFull, incl, 31);
+        tot = half ? t32 - t16 : t16;
+        if (half) incl -= t16;
+    }
+    const bool bad = (__ballot_sync(kFull, many) & hm) != 0 || tot > kRecPerStep;
+    if (!bad && nr > 0 && step < nsteps) {
+        uint32_t* out = rec + step * kRecPerStep + (incl - nr);
+        out[0] = r0;
+        if (nr > 1) out[1] = r1;
+        if (nr > 2) out[2] = r2;
+        if (nr > 3) out[3] = r3;
+        if (nr > 4) out[4] = r4;
+        if (nr > 5) out[5] = r5;
+        if (nr > 6) out[6] = r6;
+        if (nr > 7) out[7] = r7;
+    }
+    if ((lane & 15) == 0 && step < nsteps) cnt[step] = (uint8_t)(bad ? kRecOverflow : tot);
+}
+
 // The byte range to tokenize is [off[idx ? idx[0] : 0], off[idx ? idx[n] : n)): the units of this call (a chained call
-// covers a slice of the flat buffer, see QB200_CHAIN).  Bytes at and beyond the end are never read.
-//
-// A warp takes 2 KiB (two steps) per iteration: lane j loads bytes [64j, 64j+64) with four 16-byte loads (lanes 0-15
-// read the first step, lanes 16-31 the second), so one round of loop overhead, one ballot and one divergent
-// "look at the candidates" branch serve two steps, and each lane has 64 bytes in flight.
+// covers a slice of the flat buffer, see QB200_CHAIN).  A warp takes 2 KiB (two steps) per iteration.
 __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
                                                        const int64_t* __restrict__ off, const int64_t* __restrict__ idx, int64_t n,
                                                        uint8_t* __restrict__ cnt, uint32_t* __restrict__ rec, int64_t max_steps,
@@ -49,8 +133,6 @@ __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant_
     if (blockIdx.x == 0)
         for (int64_t i = threadIdx.x; i < zero_words; i += blockDim.x) zero[i] = 0;
     const int lane = threadIdx.x & 31;
-    const int half = lane >> 4;
-    const unsigned hm = half ? 0xFFFF0000u : 0x0000FFFFu;  // the lanes of this lane's step
     const int64_t begin = idx ? off[idx[0]] : off[0];
     const int64_t total = idx ? off[idx[n]] : off[n];
     int64_t nsteps = (total + 1023) >> 10;
@@ -58,87 +140,11 @@ __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant_
     const int64_t npairs = (nsteps + 1) >> 1;
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
     for (int64_t pr = (begin >> 11) + (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); pr < npairs; pr += nwarps) {
-        const int64_t a = (pr << 11) + lane * 64;
         {   // this warp's next 2 KiB: get its sixteen lines into L2 now, one iteration of work ahead of their use
             const int64_t an = ((pr + nwarps) << 11) + lane * 128;
             if (lane < 16 && an + 128 <= total) asm volatile("prefetch.global.L2 [%0];" ::"l"(bytes + an));
         }
-        uint32_t lt0 = 0, lt1 = 0;  // '<' positions in bytes [0, 32) and [32, 64) of the lane
-        if (a + 64 <= total) {
-            const uint4* p = reinterpret_cast<const uint4*>(bytes + a);
-            // plain loads, not ld.cs: the candidates' tag match re-reads these lines from L1 (measured: cfg2 0.549 -> 0.541 ms,
-            // cfg3 2.32 -> 2.27, cfg4 1.31 -> 1.29)
-            const uint4 v0 = p[0], v1 = p[1], v2 = p[2], v3 = p[3];
-            const uint32_t f0 = lt_any16(v0), f1 = lt_any16(v1), f2 = lt_any16(v2), f3 = lt_any16(v3);
-            if (f0 | f1 | f2 | f3) {  // exact positions only where needed
-                if (f0) lt0 = lt_mask16(v0);
-                if (f1) lt0 |= lt_mask16(v1) << 16;
-                if (f2) lt1 = lt_mask16(v2);
-                if (f3) lt1 |= lt_mask16(v3) << 16;
-            }
-        } else {
-            for (int b = 0; b < 32 && a + b < total; b++)
-                if (bytes[a + b] == '<') lt0 |= 1u << b;
-            for (int b = 0; b < 32 && a + 32 + b < total; b++)
-                if (bytes[a + 32 + b] == '<') lt1 |= 1u << b;
-        }
-        const unsigned any = __ballot_sync(kFull, (lt0 | lt1) != 0);
-        const int64_t step = (pr << 1) + half;
-        if (any == 0) {  // the common case: no '<' in these 2 KiB
-            if ((lane & 15) == 0 && step < nsteps) cnt[step] = 0;
-            continue;
-        }
-        // records of this lane's 64 bytes (more than 8 '<' in them is an overflow)
-        uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0, r5 = 0, r6 = 0, r7 = 0;
-        int nr = 0;
-        bool many = false;
-        unsigned long long lt = (unsigned long long)lt0 | ((unsigned long long)lt1 << 32);
-        while (lt) {
-            const int b = __ffsll((long long)lt) - 1;
-            lt &= lt - 1;
-            int is_close, cls, exotic;
-            const int len = tag_at(tg, bytes, total, a + b, is_close, cls, exotic);
-            const uint32_t r = (uint32_t)((lane & 15) * 64 + b) | ((uint32_t)len << 10) | ((len ? (uint32_t)is_close : 2u) << 17) |
-                               ((uint32_t)cls << 19) | ((uint32_t)exotic << 26);
-            if (nr == 0) r0 = r;
-            else if (nr == 1) r1 = r;
-            else if (nr == 2) r2 = r;
-            else if (nr == 3) r3 = r;
-            else if (nr == 4) r4 = r;
-            else if (nr == 5) r5 = r;
-            else if (nr == 6) r6 = r;
-            else if (nr == 7) r7 = r;
-            else many = true;
-            nr++;
-        }
-        int incl, tot;  // rank of this lane's last record inside its step, records in the step
-        if (__all_sync(kFull, nr <= 1)) {  // one record per lane at most: ranks straight from the ballot
-            incl = __popc(any & hm & (0xffffffffu >> (31 - lane)));
-            tot = __popc(any & hm);
-        } else {
-            incl = nr;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                int t = __shfl_up_sync(kFull, incl, d);
-                if (lane >= d) incl += t;
-            }
-            const int t16 = __shfl_sync(kFull, incl, 15), t32 = __shfl_sync(kFull, incl, 31);
-            tot = half ? t32 - t16 : t16;
-            if (half) incl -= t16;
-        }
-        const bool bad = (__ballot_sync(kFull, many) & hm) != 0 || tot > kRecPerStep;
-        if (!bad && nr > 0) {
-            uint32_t* out = rec + step * kRecPerStep + (incl - nr);
-            out[0] = r0;
-            if (nr > 1) out[1] = r1;
-            if (nr > 2) out[2] = r2;
-            if (nr > 3) out[3] = r3;
-            if (nr > 4) out[4] = r4;
-            if (nr > 5) out[5] = r5;
-            if (nr > 6) out[6] = r6;
-            if (nr > 7) out[7] = r7;
-        }
-        if ((lane & 15) == 0 && step < nsteps) cnt[step] = (uint8_t)(bad ? kRecOverflow : tot);
+        tokenize_pair(tg, bytes, total, nsteps, pr, lane, cnt, rec);
     }
 }
 

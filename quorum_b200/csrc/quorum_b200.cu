@@ -1,12 +1,14 @@
 // quorum_b200 — kernels + C ABI (include/quorum_b200.h).  sm_100a only; no CPU fallback.
 //
-// Default path (QB200_PATH=token), see DESIGN.md section 5.1:
+// Default path (QB200_PATH=fused, qb_fused.cuh): one persistent kernel per call, tile by tile:
+//   tokenise -> walk (lane per unit) -> scan + look-back -> offsets -> copy, the text read from HBM once.
+// Token path (QB200_PATH=token; also what units / shapes the fused kernel is not chosen for use), DESIGN.md section 5.2:
 //   stream_feed :  tokenize (one record per '<')  ->  count (lane per stream: automaton over the records, descriptor,
 //                  carried state, prefix sum over the streams by look-back)  ->  offsets (thread per feed boundary)
 //                  ->  finish (warp per stream: kept runs to their final place)
 //   strip_concat:  tokenize  ->  count (lane per response: liveness, automaton, strip(), descriptor)  ->  request layout,
 //                  scan, finalize (per-request prefix sums incl. separators)  ->  copy (warp per response)
-// QB200_PATH=general: the byte-rescanning warp-per-unit walkers (count, scan, copy); QB200_PATH=tile: qb_tile.cuh.
+// QB200_PATH=general: the byte-rescanning warp-per-unit walkers (count, scan, copy).
 // Then the rows around the filter: SSE framing (qb_sse.cuh), SSE parsing (qb_ssein.cuh), aggregate prompts (qb_agg.cuh).
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -19,7 +21,7 @@
 
 #include "../../include/quorum_b200.h"
 #include "qb_walk.cuh"
-#include "qb_tile.cuh"
+#include "qb_scan.cuh"
 #include "qb_tok.cuh"
 #include "qb_lane.cuh"
 #include "qb_sse.cuh"
@@ -435,7 +437,7 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
 //
 // SCAN: the prefix sum over the streams' released bytes (their output bases) is done here as well, single pass: a block
 // takes 256 consecutive streams by ticket, scans its totals (warp shuffles + shared memory) and gets its base by
-// decoupled look-back over the blocks before it (lookback_exclusive, qb_tile.cuh; tickets give forward progress).
+// decoupled look-back over the blocks before it (lookback_exclusive, qb_scan.cuh; tickets give forward progress).
 // scan.state / scan.ticket are zeroed by the tokenizer kernel, which runs just before on the same stream.
 struct CountScan {
     int64_t* bases;                 // out: bases[s]
@@ -688,6 +690,8 @@ __global__ void stream_flush_kernel(StreamState* st, int64_t n) {
 
 __global__ void set_i64_kernel(int64_t* p, int64_t v) { *p = v; }
 
+#include "qb_fused.cuh"
+
 // ---------------------------------------------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------------------------------------------
@@ -802,15 +806,48 @@ int qb200_tags_create(const uint8_t* names, const int32_t* name_off, int32_t n_t
 
 void qb200_tags_destroy(qb200_tags* tags) { delete tags; }
 
+// QB200_PATH selects the implementation: "fused" = single-pass tile kernels (qb_fused.cuh), "token" = tokenizer pass +
+// record-driven kernels, "general" = walkers that rescan the bytes.  Unset: fused, except for batches whose units are so
+// large that a tile would not stay in L2 between its two touches (then the token path, which is what the fused kernel
+// degenerates to anyway, minus its serial per-tile chain).
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-// QB200_PATH selects the implementation (default "token"): "token" = tokenizer pass + record-driven walkers,
-// "tile" = fused single-pass tile kernel (streams only), "general" = walkers that rescan the bytes.
+enum { kPathGeneral = 0, kPathToken = 2, kPathFused = 3, kPathAuto = 4 };
 static int path_choice() {
     const char* e = getenv("QB200_PATH");
-    if (e && strcmp(e, "general") == 0) return 0;
-    if (e && strcmp(e, "tile") == 0) return 1;
-    return 2;
+    if (e && strcmp(e, "general") == 0) return kPathGeneral;
+    if (e && strcmp(e, "token") == 0) return kPathToken;
+    if (e && strcmp(e, "fused") == 0) return kPathFused;
+    return kPathAuto;
+}
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
+// Window size of the fused kernels: the smallest power of two >= the mean unit size (from the byte bound the caller
+// states), at least 32 KiB.  Tiles then hold a handful of units and stay uniform in size.
+constexpr int kFusedMaxAutoLog2T = 16;  // auto path choice: mean unit size up to 64 KiB goes to the fused kernels
+static int fused_log2T(int64_t byte_bound, int64_t n_units) {
+    if (const int v = env_int("QB200_FUSED_LOG2T", 0)) return v < kFusedMinLog2T ? kFusedMinLog2T : (v > 30 ? 30 : v);
+    const int64_t mean = n_units > 0 ? byte_bound / n_units : 0;
+    int l = kFusedMinLog2T;
+    while (l < 30 && ((int64_t)1 << l) < mean) l++;
+    return l;
+}
+static int64_t fused_max_tiles(int64_t byte_bound) { return ((byte_bound < 0 ? 0 : byte_bound) >> kFusedMinLog2T) + 2; }
+// look-back word + first + last per tile, and the ticket
+static size_t fused_scratch_bytes(int64_t byte_bound) { return align256((size_t)fused_max_tiles(byte_bound) * 24 + 64); }
+static TileTables fused_tables(uint8_t* p, int64_t byte_bound, int log2T) {
+    const int64_t mt = fused_max_tiles(byte_bound);
+    TileTables tt;
+    tt.state = (unsigned long long*)p;
+    tt.first = (int64_t*)(p + (size_t)mt * 8);
+    tt.last = (int64_t*)(p + (size_t)mt * 16);
+    tt.ticket = (unsigned int*)(p + (size_t)mt * 24);
+    tt.max_tiles = (((byte_bound < 0 ? 0 : byte_bound) >> log2T) + 2);
+    tt.log2T = log2T;
+    return tt;
 }
 
 static int64_t steps_for(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte_bound) / 1024 + 2; }
@@ -848,7 +885,30 @@ static size_t desc_scratch_bytes(int64_t n_units) { return align256((size_t)(n_u
 static size_t stream_desc_scratch_bytes(int64_t n_units) { return align256((size_t)(n_units < 0 ? 0 : n_units) * sizeof(StreamDesc) + 96); }
 
 size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req, int64_t out_capacity) {
-    return strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp) + tok_scratch_bytes(out_capacity) + 256;
+    return strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp) + tok_scratch_bytes(out_capacity) +
+           fused_scratch_bytes(out_capacity) + 256;
+}
+
+// per-device facts, cached per device ordinal (one process may drive several GPUs)
+static int sm_count() {
+    static std::atomic<int> cache[64];
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    n = cache[dev].load(std::memory_order_relaxed);
+    if (!n) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cache[dev].store(n, std::memory_order_relaxed);
+    }
+    return n;
+}
+
+// persistent grid of the fused kernels: four CTAs per SM (their launch bounds), never more than there are windows
+static int fused_grid(int64_t max_tiles) {
+    int64_t g = 4 * (int64_t)sm_count();
+    if (const int v = env_int("QB200_GRID_CAP", 0)) g = v;  // test knob: a small grid makes every block take many tickets
+    if (g > max_tiles) g = max_tiles;
+    if (g < 1) g = 1;
+    return (int)g;
 }
 
 static int grid_for(int64_t units) {
@@ -899,11 +959,49 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
 
     TokSrc ts;
     UnitDesc* desc = (UnitDesc*)((uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req));
-    if (hide && n_resp > 0 && path_choice() != 0)
-        ts = launch_tokenizer(tags->dev, in_bytes, in_off, nullptr, n_resp, out_capacity,
-                              (uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp), stream);
+    uint8_t* tok_scratch = (uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp);
+    const int lane_steps = env_int("QB200_LANE_STEPS", 40);  // 0: warp per response only
+    const int path = path_choice();
+    const int log2T = fused_log2T(out_capacity, n_req);
+    if (n_resp > 0 && (path == kPathFused || (path == kPathAuto && log2T <= kFusedMaxAutoLog2T))) {
+        // single pass: tile map, then one persistent kernel (qb_fused.cuh)
+        uint8_t* fsp = tok_scratch + tok_scratch_bytes(out_capacity);
+        const TileTables tt = fused_tables(fsp, out_capacity, log2T);
+        CUDA_TRY(cudaMemsetAsync(fsp, 0, fused_scratch_bytes(out_capacity), stream));
+        strip_tile_map_kernel<<<(unsigned)((n_req + 255) / 256), 256, 0, stream>>>(in_off, req_off, n_req, tt);
+        LAUNCHED("strip_tile_map_kernel");
+        StripFusedParams P;
+        P.in = in_bytes;
+        P.in_off = in_off;
+        P.n_resp = n_resp;
+        P.req_off = req_off;
+        P.n_req = n_req;
+        P.sep = sep;
+        P.sep_len = sep_len;
+        P.hide = hide;
+        P.stream_join = sj;
+        P.chain = chain ? 1 : 0;
+        P.out = out_bytes;
+        P.out_off = out_off;
+        P.resp_out_len = resp_out_len;
+        P.klen = klen;
+        P.first = first;
+        P.dst = dst;
+        P.desc = desc;
+        const int64_t st = steps_for(out_capacity);
+        P.g_cnt = tok_scratch;
+        P.g_rec = (uint32_t*)(tok_scratch + align256((size_t)st));
+        P.g_max_steps = st;
+        P.tt = tt;
+        P.lane_steps = lane_steps;
+        strip_fused_kernel<<<fused_grid(tt.max_tiles), kThreads, 0, stream>>>(tags->dev, P);
+        LAUNCHED("strip_fused_kernel");
+        CUDA_TRY(cudaGetLastError());
+        return QB200_OK;
+    }
+    if (hide && n_resp > 0 && path != kPathGeneral)
+        ts = launch_tokenizer(tags->dev, in_bytes, in_off, nullptr, n_resp, out_capacity, tok_scratch, stream);
     if (hide && n_resp > 0) {
-        static const int lane_steps = getenv("QB200_LANE_STEPS") ? atoi(getenv("QB200_LANE_STEPS")) : 40;  // 0: warp per response only
         strip_count_kernel<<<grid_for((n_resp + 31) / 32), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts,
                                                                                  ts.cnt ? desc : nullptr, lane_steps);
         LAUNCHED("strip_count_kernel");
@@ -931,16 +1029,11 @@ static size_t stream_general_scratch_bytes(int64_t n_streams) {
     return 2 * align256((size_t)(n_streams + 2) * 8) + align256((size_t)(n_streams / kScanSlice + 4) * 8) + 256;
 }
 
-static int64_t tiles_for(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte_bound) / kWindow + 2; }
-
-// per tile: look-back state word + TileRec; plus the ticket
-static size_t tile_scratch_bytes(int64_t max_tiles) { return align256((size_t)(max_tiles + 1) * (8 + sizeof(TileRec)) + 64); }
-
 static size_t sid_scratch_bytes(int64_t n_chunks) { return align256((size_t)((n_chunks < 0 ? 0 : n_chunks) / kOffsetsTile + 32) * 4); }
 
 size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity) {
-    return stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity)) +
-           stream_desc_scratch_bytes(n_streams) + tok_scratch_bytes(out_capacity) + sid_scratch_bytes(n_chunks) + 256;
+    return stream_general_scratch_bytes(n_streams) + stream_desc_scratch_bytes(n_streams) + tok_scratch_bytes(out_capacity) +
+           sid_scratch_bytes(n_chunks) + fused_scratch_bytes(out_capacity) + 256;
 }
 
 static int stream_feed_check(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
@@ -986,8 +1079,8 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     size_t sid_offset = 0;
     unsigned long long* scan_state = nullptr;
     unsigned int* scan_ticket = nullptr;
-    if (use_tokens) {  // descriptors + records (+ the chunk -> stream map) live behind the general + tile scratch regions
-        uint8_t* tsp = (uint8_t*)scratch + stream_general_scratch_bytes(n_streams) + tile_scratch_bytes(tiles_for(out_capacity));
+    if (use_tokens) {  // descriptors + records (+ the chunk -> stream map) live behind the general scratch region
+        uint8_t* tsp = (uint8_t*)scratch + stream_general_scratch_bytes(n_streams);
         desc = (StreamDesc*)tsp;
         scan_state = (unsigned long long*)totals;  // (n_streams / 256 + 2) words + the ticket fit in the totals array
         const int64_t nblk = (n_streams + 255) / 256 + 1;
@@ -997,7 +1090,7 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
         sid_offset = (size_t)(tsp - (uint8_t*)scratch) + stream_desc_scratch_bytes(n_streams) + tok_scratch_bytes(out_capacity);
     }
     int32_t* sid = use_tokens ? (int32_t*)((uint8_t*)scratch + sid_offset) : nullptr;
-    static const int lane_steps = getenv("QB200_LANE_STEPS") ? atoi(getenv("QB200_LANE_STEPS")) : 40;  // 0: warp per stream only
+    const int lane_steps = env_int("QB200_LANE_STEPS", 40);  // 0: warp per stream only
     // chained call: this call's output starts where out_chunk_off[first chunk of the call] says (written by the call before)
     if (use_tokens) {  // prefix sum inside the count kernel (look-back words live where the totals would)
         CountScan cs{bases, scan_state, scan_ticket, chain ? out_chunk_off : nullptr, chain ? stream_off : nullptr};
@@ -1032,24 +1125,16 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     return QB200_OK;
 }
 
-static int g_sm_count = 0;
-static int sm_count() {
-    if (!g_sm_count) {
-        int dev = 0, n = 148;
-        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-        g_sm_count = n > 0 ? n : 148;
-    }
-    return g_sm_count;
-}
-
 int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
                             const int64_t* stream_off, int64_t n_streams, const qb200_stream_state* state_in,
                             qb200_stream_state* state_out, uint32_t flags, uint8_t* out_bytes, int64_t out_capacity,
                             int64_t* out_chunk_off, void* scratch, size_t scratch_bytes, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     const int path = path_choice();
-    if (path != 1 || n_streams == 0 || (flags & QB200_CHAIN)) {
-        const bool tok = path == 2 && n_streams > 0;
+    const int log2T = fused_log2T(out_capacity, n_streams);
+    const bool fused = n_streams > 0 && (path == kPathFused || (path == kPathAuto && log2T <= kFusedMaxAutoLog2T));
+    if (!fused) {
+        const bool tok = path != kPathGeneral && n_streams > 0;
         if (tok && (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams, out_capacity) || !scratch))
             return fail(QB200_ESCRATCH, "stream_feed_batch: scratch too small (see qb200_stream_feed_scratch_bytes)");
         return stream_feed_general(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, state_in, state_out, flags,
@@ -1060,10 +1145,10 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
     if (rc != QB200_OK) return rc;
     if (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams, out_capacity) || !scratch)
         return fail(QB200_ESCRATCH, "stream_feed_batch: scratch too small (see qb200_stream_feed_scratch_bytes)");
-    // Fused single-pass path.  scratch: totals | bases (general walkers inside the kernel) | tile states + ticket (zeroed)
+    // single pass: tile map, then one persistent kernel (qb_fused.cuh).  scratch: totals (unused) | bases | ... | descriptors |
+    // records | stream map (unused) | tile tables
     uint8_t* sp = (uint8_t*)scratch;
-    StreamTileParams P;
-    P.tg = tags->dev;
+    StreamFusedParams P;
     P.bytes = chunk_bytes;
     P.chunk_off = chunk_off;
     P.n_chunks = n_chunks;
@@ -1072,31 +1157,25 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
     P.st_in = reinterpret_cast<const StreamState*>(state_in);
     P.st_out = reinterpret_cast<StreamState*>(state_out);
     P.flags = flags;
+    P.chain = (flags & QB200_CHAIN) ? 1 : 0;
     P.out = out_bytes;
     P.out_chunk_off = out_chunk_off;
-    P.unit_totals = (int64_t*)sp;
-    sp += align256((size_t)(n_streams + 2) * 8);
-    P.unit_bases = (int64_t*)sp;
-    sp += align256((size_t)(n_streams + 2) * 8);
-    const int64_t max_tiles = tiles_for(out_capacity);
-    P.tile_state = (unsigned long long*)sp;
-    TileRec* rec = (TileRec*)(P.tile_state + ((max_tiles + 1) & ~(int64_t)1));  // 16-byte aligned
-    P.rec = rec;
-    P.ticket = (unsigned int*)(rec + max_tiles);
-    P.max_tiles = max_tiles;
-    CUDA_TRY(cudaMemsetAsync(P.tile_state, 0, tile_scratch_bytes(max_tiles), stream));
-    stream_tile_map_kernel<<<(unsigned)((n_streams + 255) / 256), 256, 0, stream>>>(chunk_off, n_chunks, stream_off, n_streams,
-                                                                                   rec, max_tiles);
+    P.bases = (int64_t*)(sp + align256((size_t)(n_streams + 2) * 8));
+    uint8_t* tsp = sp + stream_general_scratch_bytes(n_streams);
+    P.desc = (StreamDesc*)tsp;
+    uint8_t* tok_scratch = tsp + stream_desc_scratch_bytes(n_streams);
+    const int64_t st = steps_for(out_capacity);
+    P.g_cnt = tok_scratch;
+    P.g_rec = (uint32_t*)(tok_scratch + align256((size_t)st));
+    P.g_max_steps = st;
+    uint8_t* fsp = tok_scratch + tok_scratch_bytes(out_capacity) + sid_scratch_bytes(n_chunks);
+    P.tt = fused_tables(fsp, out_capacity, log2T);
+    P.lane_steps = env_int("QB200_LANE_STEPS", 40);
+    CUDA_TRY(cudaMemsetAsync(fsp, 0, fused_scratch_bytes(out_capacity), stream));
+    stream_tile_map_kernel<<<(unsigned)((n_streams + 255) / 256), 256, 0, stream>>>(chunk_off, stream_off, n_streams, P.tt);
     LAUNCHED("stream_tile_map_kernel");
-    static bool attr_set = false;
-    if (!attr_set) {
-        CUDA_TRY(cudaFuncSetAttribute(stream_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileShared)));
-        attr_set = true;
-    }
-    int64_t grid = 4 * (int64_t)sm_count();
-    if (grid > max_tiles) grid = max_tiles;
-    stream_tile_kernel<<<(unsigned)grid, kTileThreads, sizeof(TileShared), stream>>>(P);
-    LAUNCHED("stream_tile_kernel");
+    stream_fused_kernel<<<fused_grid(P.tt.max_tiles), kThreads, 0, stream>>>(tags->dev, P);
+    LAUNCHED("stream_fused_kernel");
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
 }

@@ -146,46 +146,86 @@ def parse_http_chunks(chunks: Sequence[bytes], device=None) -> List[Optional[Lis
     return res
 
 
+def parse_http_chunks_ex(chunks: Sequence[bytes], device=None) -> List[Tuple[Optional[List[str]], bool]]:
+    """parse_sse_events (quorum_b200/streaming.py) over a batch of HTTP chunks on the device: per chunk (deltas, ended).
+    A chunk with an event the device parser is not certain about (kind 2) is parsed by the host function instead."""
+    from .streaming import parse_sse_events
+    from .filter import _dec
+    if not chunks:
+        return []
+    dev = _device(device)
+    data, off = _b.pack_host([bytes(c) for c in chunks])
+    d_data = _to_device(data if data.numel() else torch.zeros(16, dtype=torch.uint8), dev)
+    out, out_off, kind, ev_first, n_host = parse_http_chunks_device(d_data, _to_device(off, dev))
+    first = ev_first.cpu().tolist()
+    kinds = kind.cpu().numpy()
+    pieces = _b.split_host(out, out_off)
+    res: List[Tuple[Optional[List[str]], bool]] = []
+    for c, chunk in enumerate(chunks):
+        a, b = first[c], first[c + 1]
+        if a == b:
+            res.append((None, False))
+        elif (kinds[a:b] == 2).any():
+            res.append(parse_sse_events(bytes(chunk)))
+        else:
+            res.append(([_dec(pieces[k]) for k in range(a, b) if kinds[k] == 1], False))
+    return res
+
+
 # ---- the whole streaming step on the device: HTTP chunks in, SSE events out ---------------------------------------------
 
 class DeviceStreamPipeline:
     """What progress_streaming_aggregator does per HTTP chunk of every backend (oai_proxy.py:578-652), batched over
     `n_streams` streams with the data staying on the device between the three steps: parse the chunks (row f2), feed the
     deltas through the ThinkingTagFilter of their stream with carried state (a3), frame every non-empty filtered delta
-    as the reference's SSE event (f1).  `backend_of_stream[s]` is the i of `chatcmpl-parallel-{i}` for stream s."""
+    as the reference's SSE event (f1).  `backend_of_stream[s]` is the i of `chatcmpl-parallel-{i}` for stream s.
+    `created` is the event time stamp; the reference stamps every event with int(loop.time()) (oai_proxy.py:634), so pass
+    the current value to step() when it matters (the constructor's value is the default)."""
 
     def __init__(self, thinking_tags: Sequence[str], backend_of_stream: Sequence[int], created: int, device=None,
-                 hide_intermediate_think: bool = True):
+                 hide_intermediate_think: bool = True, suppress_individual_responses: bool = False):
         self.dev = _device(device)
         self.n = len(backend_of_stream)
         self.table = _b.tag_table(list(thinking_tags))
         self.hide = hide_intermediate_think
+        self.suppress = suppress_individual_responses
+        self.created = created
         self.state = _b.new_stream_state(self.n, self.dev)
-        ids = sorted(set(int(i) for i in backend_of_stream))
-        slot = {i: k for k, i in enumerate(ids)}
-        env = [event_envelope(backend_event_id(i), created) for i in ids]
-        self.prefixes, self.suffix = [e[0] for e in env], env[0][1]
+        self.ids = sorted(set(int(i) for i in backend_of_stream))
+        slot = {i: k for k, i in enumerate(self.ids)}
         self.slot_of_stream = torch.tensor([slot[int(i)] for i in backend_of_stream], dtype=torch.int32).to(self.dev)
         self.content = [[] for _ in range(self.n)]  # filtered bytes per stream, for the final join (oai_proxy.py:624)
+        self.ended = [False] * self.n               # stream ended by an exception (oai_proxy.py:660-673): contributes nothing
 
-    def step(self, chunks: Sequence[Optional[bytes]]) -> List[List[bytes]]:
+    def abandon(self, s: int) -> None:
+        """The stream's chunk iterator raised: nothing more is read from it, its content never reaches the final join."""
+        self.ended[s] = True
+
+    def step(self, chunks: Sequence[Optional[bytes]], created: Optional[int] = None) -> List[List[bytes]]:
         """chunks[s] = the HTTP chunk that arrived for stream s (None: nothing).  Returns, per stream, the SSE events to
         send on, in order."""
-        from .streaming import parse_sse_chunk
+        from .streaming import parse_sse_events
         if len(chunks) != self.n:
             raise ValueError("one entry per stream")
         dev = self.dev
-        data, off = _b.pack_host([bytes(c) if c is not None else b"" for c in chunks])
+        created = self.created if created is None else created
+        env = [event_envelope(backend_event_id(i), created) for i in self.ids]
+        prefixes, suffix = [e[0] for e in env], env[0][1]
+        live = [bytes(c) if (c is not None and not self.ended[s]) else b"" for s, c in enumerate(chunks)]
+        data, off = _b.pack_host(live)
         d_data = _to_device(data if data.numel() else torch.zeros(16, dtype=torch.uint8), dev)
         out, out_off, kind, ev_first, n_host = parse_http_chunks_device(d_data, _to_device(off, dev))
         if int(n_host.item()):  # an event the device is not certain about: those chunks go through the reference's code path
             first, kinds = ev_first.cpu().tolist(), kind.cpu().numpy()
             pieces = _b.split_host(out, out_off)
             deltas = []
-            for s, c in enumerate(chunks):
+            for s, c in enumerate(live):
                 a, b = first[s], first[s + 1]
-                if c is not None and (kinds[a:b] == 2).any():
-                    deltas.append([_enc(t) for t in (parse_sse_chunk(bytes(c)) or [])])
+                if (kinds[a:b] == 2).any():
+                    ds, ended = parse_sse_events(c)     # the events before a raising one still count; the stream is over
+                    deltas.append([_enc(t) for t in (ds or [])])
+                    if ended:
+                        self.ended[s] = True
                 else:
                     deltas.append([pieces[k] for k in range(a, b) if kinds[k] == 1])
             flat = [d for ds in deltas for d in ds]
@@ -200,13 +240,16 @@ class DeviceStreamPipeline:
             f_bytes, f_off, self.state = _b.stream_feed_batch(self.table, out, out_off, ev_first, self.state, state_out=self.state)
         else:
             f_bytes, f_off = out, out_off
-        # the stream of every event: events are grouped by stream in order
-        counts = ev_first[1:] - ev_first[:-1]
-        ev_slot = torch.repeat_interleave(self.slot_of_stream, counts, output_size=n_events)
-        framed, framed_off = frame_events_device(f_bytes, f_off, ev_slot, self.prefixes, self.suffix, skip_empty=True)
         first = ev_first.cpu().tolist()
-        events = _b.split_host(framed, framed_off)
         texts = _b.split_host(f_bytes, f_off)
+        if self.suppress:   # oai_proxy.py:625-628: nothing is sent per delta, the content still accumulates
+            events = [b""] * n_events
+        else:
+            # the stream of every event: events are grouped by stream in order
+            counts = ev_first[1:] - ev_first[:-1]
+            ev_slot = torch.repeat_interleave(self.slot_of_stream, counts, output_size=n_events)
+            framed, framed_off = frame_events_device(f_bytes, f_off, ev_slot, prefixes, suffix, skip_empty=True)
+            events = _b.split_host(framed, framed_off)
         res: List[List[bytes]] = []
         for s in range(self.n):
             a, b = first[s], first[s + 1]
@@ -215,7 +258,23 @@ class DeviceStreamPipeline:
         return res
 
     def finish(self) -> List[str]:
-        """flush() every filter (oai_proxy.py:739-741: returns "", drops a held partial) and return each stream's content."""
+        """flush() every filter (oai_proxy.py:739-741: returns "", drops a held partial) and return each stream's content
+        ("" for a stream that ended in an exception: the reference never stores it)."""
         from .filter import _dec
         _b.stream_flush_batch(self.state)
-        return [_dec(b"".join(c)) for c in self.content]
+        return ["" if self.ended[s] else _dec(b"".join(c)) for s, c in enumerate(self.content)]
+
+
+def tail_events_device(strategy, contents: Sequence[str], created: int, device=None) -> List[bytes]:
+    """What follows the last backend (oai_proxy.py:759-885) with the join and the framing on the device: the final event
+    (strip_thinking_tags + join by qb200_strip_concat_batch, event by qb200_sse_frame_batch), or the error event when no
+    backend has content, nothing when skip_final_aggregation; then `[DONE]`."""
+    from . import streaming as st
+    out: List[bytes] = []
+    if not strategy.skip_final_aggregation:
+        if any(contents):
+            out.append(frame_final_event(strategy.combine_stream_final(contents), created, device))
+        else:
+            out.append(st.error_event(created))
+    out.append(st.DONE_EVENT)
+    return out

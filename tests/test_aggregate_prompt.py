@@ -34,8 +34,8 @@ def test_oracle_usage_sums():
 
 @pytest.mark.gpu
 def test_gpu_prompts_match_reference_prompts():
-    """The reference passes already filtered answers to aggregate_responses; hide_intermediate_think=False keeps the
-    builder's filter out of the way so the golden prompts apply as they are (grouped by configuration: one batch each)."""
+    """The reference passes already filtered answers to aggregate_responses; hide_final_think=False (the reference's
+    default) keeps the builder's filter out of the way so the golden prompts apply as they are (grouped by configuration: one batch each)."""
     import quorum_b200 as qb
     groups = {}
     for c in _cases():
@@ -43,7 +43,7 @@ def test_gpu_prompts_match_reference_prompts():
         groups.setdefault(key, []).append(c)
     for key, cs in groups.items():
         b = qb.AggregatePromptBuilder(separator=key[0], include_original_query=key[1], query_format=key[2], include_source_names=key[3],
-                                      source_label_format=key[4], prompt_template=key[5], hide_intermediate_think=False)
+                                      source_label_format=key[4], prompt_template=key[5], hide_final_think=False)
         got = b.build_prompts([c["responses"] for c in cs], [c["query"] for c in cs])
         for c, g in zip(cs, got):
             assert g == c["expect"], c
@@ -60,9 +60,10 @@ def test_gpu_prompts_with_filter_match_oracle():
     for _ in range(200):
         reqs.append(["".join(rng.choice(pieces) for _ in range(rng.randrange(0, 30))) for _ in range(rng.randrange(1, 6))])
         queries.append("".join(rng.choice(pieces) for _ in range(rng.randrange(0, 5))))
-    b = qb.AggregatePromptBuilder.from_config({"strategy": {"aggregate": {"include_source_names": True,
+    b = qb.AggregatePromptBuilder.from_config({"strategy": {"aggregate": {"include_source_names": True, "thinking_tags": tags,
+                                                                           "hide_final_think": True,
                                                                            "prompt_template": "T: {intermediate_results} :end"}},
-                                               "iterations": {"aggregation": {"thinking_tags": tags}}})
+                                               "iterations": {"aggregation": {"strategy": "aggregate"}}})
     got = b.build_prompts(reqs, queries)
     for cs, q, g in zip(reqs, queries, got):
         filtered = [o.strip_thinking_tags(c, tags, True) for c in cs]

@@ -351,4 +351,69 @@ __device__ inline void warp_copy(uint8_t* dst, const uint8_t* src, int64_t n, co
     for (int64_t i = (nvec << 4) + lane; i < n; i += 32) dst[i] = src[i];
 }
 
+// Lean variant for the kept runs of a unit (lengths below 2 GiB, typically 0.1-4 KiB): 32-bit arithmetic, and the word
+// select of the realignment hoisted out of the loop (one loop per word offset) - the general warp_copy above spends
+// ~300 warp instructions per call before and after its loops, which is most of the cost of a 1 KiB run.
+template <int W>
+__device__ __forceinline__ uint4 realign_w(const uint4& A, const uint4& B, int sh) {
+    uint32_t w0, w1, w2, w3, w4;
+    if (W == 0) { w0 = A.x; w1 = A.y; w2 = A.z; w3 = A.w; w4 = B.x; }
+    else if (W == 1) { w0 = A.y; w1 = A.z; w2 = A.w; w3 = B.x; w4 = B.y; }
+    else if (W == 2) { w0 = A.z; w1 = A.w; w2 = B.x; w3 = B.y; w4 = B.z; }
+    else { w0 = A.w; w1 = B.x; w2 = B.y; w3 = B.z; w4 = B.w; }
+    uint4 o;
+    o.x = __funnelshift_r(w0, w1, sh);
+    o.y = __funnelshift_r(w1, w2, sh);
+    o.z = __funnelshift_r(w2, w3, sh);
+    o.w = __funnelshift_r(w3, w4, sh);
+    return o;
+}
+template <int W>
+__device__ __forceinline__ void copy_vecs_w(uint4* __restrict__ d4, const uint4* __restrict__ s4, int nvec, int sh, int lane) {
+    int v = lane;
+    for (; v + 32 < nvec; v += 64) {  // two rounds (four loads) in flight before the first store waits
+        const uint4 a0 = s4[v], b0 = s4[v + 1], a1 = s4[v + 32], b1 = s4[v + 33];
+        d4[v] = realign_w<W>(a0, b0, sh);
+        d4[v + 32] = realign_w<W>(a1, b1, sh);
+    }
+    if (v < nvec) {
+        const uint4 a0 = s4[v], b0 = s4[v + 1];
+        d4[v] = realign_w<W>(a0, b0, sh);
+    }
+}
+__device__ __forceinline__ void warp_copy_fast(uint8_t* dst, const uint8_t* src, int n, const uint8_t* src_hi, int lane) {
+    if (n <= 0) return;
+    int head = (int)((16u - (uint32_t)reinterpret_cast<uintptr_t>(dst)) & 15u);
+    if (head > n) head = n;
+    if (lane < head) dst[lane] = src[lane];
+    dst += head;
+    src += head;
+    n -= head;
+    const int shift = (int)(reinterpret_cast<uintptr_t>(src) & 15);
+    const uint4* s4 = reinterpret_cast<const uint4*>(src - shift);
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+    int nvec = n >> 4;
+    if (shift == 0) {
+        int v = lane;
+        for (; v + 32 < nvec; v += 64) {
+            const uint4 a0 = s4[v], a1 = s4[v + 32];
+            d4[v] = a0;
+            d4[v + 32] = a1;
+        }
+        if (v < nvec) d4[v] = s4[v];
+    } else {
+        // the realigning read touches the next 16-byte vector: keep that inside [.., src_hi)
+        const int64_t room = (src_hi - reinterpret_cast<const uint8_t*>(s4)) >> 4;  // whole vectors readable
+        if ((int64_t)nvec + 1 > room) nvec = room > 0 ? (int)(room - 1) : 0;
+        const int sh = (shift & 3) * 8;
+        switch (shift >> 2) {
+            case 0: copy_vecs_w<0>(d4, s4, nvec, sh, lane); break;
+            case 1: copy_vecs_w<1>(d4, s4, nvec, sh, lane); break;
+            case 2: copy_vecs_w<2>(d4, s4, nvec, sh, lane); break;
+            default: copy_vecs_w<3>(d4, s4, nvec, sh, lane); break;
+        }
+    }
+    for (int i = (nvec << 4) + lane; i < n; i += 32) dst[i] = src[i];
+}
+
 }  // namespace qb

@@ -35,13 +35,27 @@ __device__ __forceinline__ int tag_at(const DevTags& tg, const uint8_t* buf, int
 
 __device__ __forceinline__ uint32_t lt_any16(const uint4& v) { return lt_any(v.x) | lt_any(v.y) | lt_any(v.z) | lt_any(v.w); }
 
+// Per-warp scratch of the tokenizer (shared memory): the candidate list of a dense pair.
+constexpr int kTokList = 2 * kRecPerStep;
+struct TokWarpScratch {
+    uint16_t list[kTokList];   // positions (inside the 2 KiB pair) of the '<' candidates, in position order
+};
+
 // One 2 KiB pair of steps `pr` of the flat buffer, by one warp: lane j loads bytes [64j, 64j+64) with four 16-byte loads
 // (lanes 0-15 read the first step, lanes 16-31 the second), so one ballot and one divergent "look at the candidates"
-// branch serve two steps, and each lane has 64 bytes in flight.  cnt / rec are indexed by absolute step (the caller may
-// pass pointers shifted so that the steps of a tile land in shared memory); steps >= nsteps are not written, bytes at and
-// beyond `total` are never read.
+// branch serve two steps, and each lane has 64 bytes in flight.
+//   sparse pair (no lane has more than one '<', the usual case): every lane with a candidate matches it, ranks straight
+//     from the ballot;
+//   dense pair: the candidates are written, in position order, to a list in shared memory (ranks from a warp scan of the
+//     per-lane counts) and matched ONE PER LANE, so the expensive part (tag_at) runs once per 32 candidates instead of
+//     once per candidate of the busiest lane (adversarial text has 40 '<' per KiB in places: cfg5's tokenizer 1.16 ->
+//     0.65 ms); a candidate's record goes straight to its slot: its rank inside its step is its list index minus the
+//     step's first index.
+// cnt / rec are indexed by absolute step (the caller may pass pointers shifted so that the steps of a tile land in shared
+// memory); steps >= nsteps are not written, bytes at and beyond `total` are never read.  A step with more than
+// kRecPerStep candidates gets cnt = kRecOverflow and no records.
 __device__ __forceinline__ void tokenize_pair(const DevTags& tg, const uint8_t* __restrict__ bytes, int64_t total, int64_t nsteps,
-                                              int64_t pr, int lane, uint8_t* cnt, uint32_t* rec) {
+                                              int64_t pr, int lane, uint8_t* cnt, uint32_t* rec, TokWarpScratch& W) {
     const int half = lane >> 4;
     const unsigned hm = half ? 0xFFFF0000u : 0x0000FFFFu;  // the lanes of this lane's step
     const int64_t a = (pr << 11) + lane * 64;
@@ -70,57 +84,56 @@ __device__ __forceinline__ void tokenize_pair(const DevTags& tg, const uint8_t* 
         if ((lane & 15) == 0 && step < nsteps) cnt[step] = 0;
         return;
     }
-    // records of this lane's 64 bytes (more than 8 '<' in them is an overflow)
-    uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0, r5 = 0, r6 = 0, r7 = 0;
-    int nr = 0;
-    bool many = false;
-    unsigned long long lt = (unsigned long long)lt0 | ((unsigned long long)lt1 << 32);
-    while (lt) {
-        const int b = __ffsll((long long)lt) - 1;
-        lt &= lt - 1;
-        int is_close, cls, exotic;
-        const int len = tag_at(tg, bytes, total, a + b, is_close, cls, exotic);
-        const uint32_t r = (uint32_t)((lane & 15) * 64 + b) | ((uint32_t)len << 10) | ((len ? (uint32_t)is_close : 2u) << 17) |
-                           ((uint32_t)cls << 19) | ((uint32_t)exotic << 26);
-        if (nr == 0) r0 = r;
-        else if (nr == 1) r1 = r;
-        else if (nr == 2) r2 = r;
-        else if (nr == 3) r3 = r;
-        else if (nr == 4) r4 = r;
-        else if (nr == 5) r5 = r;
-        else if (nr == 6) r6 = r;
-        else if (nr == 7) r7 = r;
-        else many = true;
-        nr++;
-    }
-    int incl, tot;  // rank of this lane's last record inside its step, records in the step
-    if (__all_sync(kFull, nr <= 1)) {  // one record per lane at most: ranks straight from the ballot
-        incl = __popc(any & hm & (0xffffffffu >> (31 - lane)));
-        tot = __popc(any & hm);
-    } else {
-        incl = nr;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int t = __shfl_up_sync(kFull, incl, d);
-            if (lane >= d) incl += t;
+    const int nr = __popc(lt0) + __popc(lt1);
+    if (__all_sync(kFull, nr <= 1)) {  // sparse: one record per lane at most, ranks straight from the ballot
+        const int tot = __popc(any & hm);
+        if (nr) {
+            const int b = lt0 ? __ffs(lt0) - 1 : 32 + __ffs(lt1) - 1;
+            int is_close, cls, exotic;
+            const int len = tag_at(tg, bytes, total, a + b, is_close, cls, exotic);
+            const uint32_t r = (uint32_t)((lane & 15) * 64 + b) | ((uint32_t)len << 10) | ((len ? (uint32_t)is_close : 2u) << 17) |
+                               ((uint32_t)cls << 19) | ((uint32_t)exotic << 26);
+            if (step < nsteps) rec[step * kRecPerStep + __popc(any & hm & (0xffffffffu >> (31 - lane))) - 1] = r;
         }
-        const int t16 = __shfl_sync(kFull, incl, 15), t32 = __shfl_sync(kFull, incl, 31);
-        tot = half ? t32 - t16 : t16;
-        if (half) incl -= t16;
+        if ((lane & 15) == 0 && step < nsteps) cnt[step] = (uint8_t)tot;  // at most 16
+        return;
     }
-    const bool bad = (__ballot_sync(kFull, many) & hm) != 0 || tot > kRecPerStep;
-    if (!bad && nr > 0 && step < nsteps) {
-        uint32_t* out = rec + step * kRecPerStep + (incl - nr);
-        out[0] = r0;
-        if (nr > 1) out[1] = r1;
-        if (nr > 2) out[2] = r2;
-        if (nr > 3) out[3] = r3;
-        if (nr > 4) out[4] = r4;
-        if (nr > 5) out[5] = r5;
-        if (nr > 6) out[6] = r6;
-        if (nr > 7) out[7] = r7;
+    // dense: ranks from a warp scan, candidates compacted into the list, one per lane per round
+    int incl = nr;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(kFull, incl, d);
+        if (lane >= d) incl += t;
     }
-    if ((lane & 15) == 0 && step < nsteps) cnt[step] = (uint8_t)(bad ? kRecOverflow : tot);
+    const int c0 = __shfl_sync(kFull, incl, 15), c1 = __shfl_sync(kFull, incl, 31) - c0;  // candidates of the two steps
+    const bool bad0 = c0 > kRecPerStep, bad1 = c1 > kRecPerStep;
+    const int first1 = bad0 ? 0 : c0;                 // list index of the second step's first candidate
+    const int n_list = first1 + (bad1 ? 0 : c1);
+    {
+        const bool bad = half ? bad1 : bad0;
+        int idx = half ? first1 + (incl - nr - c0) : incl - nr;
+        if (!bad) {
+            unsigned long long m = (unsigned long long)lt0 | ((unsigned long long)lt1 << 32);
+            while (m) {
+                const int b = __ffsll((long long)m) - 1;
+                m &= m - 1;
+                W.list[idx++] = (uint16_t)(lane * 64 + b);
+            }
+        }
+    }
+    __syncwarp();
+    for (int i = lane; i < n_list; i += 32) {
+        const int pos = W.list[i];
+        const int sl = pos >> 10;
+        int is_close, cls, exotic;
+        const int len = tag_at(tg, bytes, total, (pr << 11) + pos, is_close, cls, exotic);
+        const uint32_t r = (uint32_t)(pos & 1023) | ((uint32_t)len << 10) | ((len ? (uint32_t)is_close : 2u) << 17) |
+                           ((uint32_t)cls << 19) | ((uint32_t)exotic << 26);
+        const int64_t st = (pr << 1) + sl;
+        if (st < nsteps) rec[st * kRecPerStep + (i - (sl ? first1 : 0))] = r;
+    }
+    if ((lane & 15) == 0 && step < nsteps) cnt[step] = (uint8_t)((half ? bad1 : bad0) ? kRecOverflow : (half ? c1 : c0));
+    __syncwarp();
 }
 
 // The byte range to tokenize is [off[idx ? idx[0] : 0], off[idx ? idx[n] : n)): the units of this call (a chained call
@@ -129,6 +142,7 @@ __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant_
                                                        const int64_t* __restrict__ off, const int64_t* __restrict__ idx, int64_t n,
                                                        uint8_t* __restrict__ cnt, uint32_t* __restrict__ rec, int64_t max_steps,
                                                        unsigned long long* __restrict__ zero, int64_t zero_words) {
+    __shared__ TokWarpScratch s_tok[8];
     // housekeeping for the kernel that follows on the stream: its look-back words and ticket start at zero
     if (blockIdx.x == 0)
         for (int64_t i = threadIdx.x; i < zero_words; i += blockDim.x) zero[i] = 0;
@@ -144,7 +158,7 @@ __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant_
             const int64_t an = ((pr + nwarps) << 11) + lane * 128;
             if (lane < 16 && an + 128 <= total) asm volatile("prefetch.global.L2 [%0];" ::"l"(bytes + an));
         }
-        tokenize_pair(tg, bytes, total, nsteps, pr, lane, cnt, rec);
+        tokenize_pair(tg, bytes, total, nsteps, pr, lane, cnt, rec, s_tok[threadIdx.x >> 5]);
     }
 }
 

@@ -384,7 +384,7 @@ __device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, con
     }
     for (int i = 0; i < nruns; i++) {
         const int s_i = __shfl_sync(kFull, rs, i), l_i = __shfl_sync(kFull, len, i), o_i = __shfl_sync(kFull, off, i);
-        if (l_i > 0) warp_copy<true>(dst + o_i, src + s_i, l_i, src_hi, lane);
+        if (l_i > 0) warp_copy_fast(dst + o_i, src + s_i, l_i, src_hi, lane);
     }
 }
 
@@ -825,27 +825,32 @@ static int env_int(const char* name, int dflt) {
     return e ? atoi(e) : dflt;
 }
 
-// Window size of the fused kernels: the smallest power of two >= the mean unit size (from the byte bound the caller
-// states), at least 32 KiB.  Tiles then hold a handful of units and stay uniform in size.
-constexpr int kFusedMaxAutoLog2T = 16;  // auto path choice: mean unit size up to 64 KiB goes to the fused kernels
+// Window size of the fused kernels: 16 KiB (what a warp's shared record slice covers), 8 KiB when the units are small
+// (more units per tile than that is no gain, and a shorter tile has a shorter chain).  Larger units simply span several
+// windows; their records then go to the global arrays.
+constexpr int64_t kFusedMaxAutoMean = 65536;  // auto path choice: mean unit size up to 64 KiB goes to the fused kernels
+static int64_t mean_unit_bytes(int64_t byte_bound, int64_t n_units) { return n_units > 0 ? byte_bound / n_units : 0; }
 static int fused_log2T(int64_t byte_bound, int64_t n_units) {
     if (const int v = env_int("QB200_FUSED_LOG2T", 0)) return v < kFusedMinLog2T ? kFusedMinLog2T : (v > 30 ? 30 : v);
-    const int64_t mean = n_units > 0 ? byte_bound / n_units : 0;
-    int l = kFusedMinLog2T;
-    while (l < 30 && ((int64_t)1 << l) < mean) l++;
-    return l;
+    return mean_unit_bytes(byte_bound, n_units) >= 12288 ? 14 : 13;
 }
-static int64_t fused_max_tiles(int64_t byte_bound) { return ((byte_bound < 0 ? 0 : byte_bound) >> kFusedMinLog2T) + 2; }
-// look-back word + first + last per tile, and the ticket
-static size_t fused_scratch_bytes(int64_t byte_bound) { return align256((size_t)fused_max_tiles(byte_bound) * 24 + 64); }
+static int64_t fused_max_tiles(int64_t byte_bound, int log2T) { return ((byte_bound < 0 ? 0 : byte_bound) >> log2T) + 2; }
+// per tile: its record (64 B) and its look-back word; per group of 32 tiles: a look-back word.  Sized for the smallest
+// window; a call lays the tables out for its own window size and clears only that part.
+static size_t fused_table_bytes(int64_t byte_bound, int log2T) {
+    const int64_t mt = fused_max_tiles(byte_bound, log2T), mg = mt / 32 + 2;
+    return align256((size_t)mt * 72 + (size_t)mg * 8 + 64);
+}
+static size_t fused_scratch_bytes(int64_t byte_bound) { return fused_table_bytes(byte_bound, kFusedMinLog2T); }
 static TileTables fused_tables(uint8_t* p, int64_t byte_bound, int log2T) {
-    const int64_t mt = fused_max_tiles(byte_bound);
+    const int64_t mt = fused_max_tiles(byte_bound, log2T);
     TileTables tt;
-    tt.state = (unsigned long long*)p;
-    tt.first = (int64_t*)(p + (size_t)mt * 8);
-    tt.last = (int64_t*)(p + (size_t)mt * 16);
-    tt.ticket = (unsigned int*)(p + (size_t)mt * 24);
-    tt.max_tiles = (((byte_bound < 0 ? 0 : byte_bound) >> log2T) + 2);
+    tt.rec = (TileRec*)p;
+    p += (size_t)mt * 64;
+    tt.lb.state = (unsigned long long*)p;
+    p += (size_t)mt * 8;
+    tt.lb.gstate = (unsigned long long*)p;
+    tt.max_tiles = mt;
     tt.log2T = log2T;
     return tt;
 }
@@ -902,11 +907,22 @@ static int sm_count() {
     return n;
 }
 
-// persistent grid of the fused kernels: four CTAs per SM (their launch bounds), never more than there are windows
-static int fused_grid(int64_t max_tiles) {
-    int64_t g = 4 * (int64_t)sm_count();
-    if (const int v = env_int("QB200_GRID_CAP", 0)) g = v;  // test knob: a small grid makes every block take many tickets
-    if (g > max_tiles) g = max_tiles;
+// Grid of the fused kernels: every CTA must be resident at once (tiles are dealt statically and a tile waits, in its
+// look-back, for tiles that other warps hold), so the size comes from the occupancy calculator and the launch is a
+// cooperative one, which fails instead of deadlocking if the grid would not fit.  Cached per device and kernel.
+static int fused_grid(const void* kernel, int which, int64_t max_tiles) {
+    static std::atomic<int> cache[64][2];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    int per_sm = cache[dev][which].load(std::memory_order_relaxed);
+    if (!per_sm) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+        cache[dev][which].store(per_sm, std::memory_order_relaxed);
+    }
+    int64_t g = (int64_t)per_sm * sm_count();
+    if (const int v = env_int("QB200_GRID_CAP", 0)) g = v < g ? v : g;  // test knob: a small grid makes every warp loop over many tiles
+    const int64_t need = (max_tiles + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    if (g > need) g = need;
     if (g < 1) g = 1;
     return (int)g;
 }
@@ -963,11 +979,11 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     const int lane_steps = env_int("QB200_LANE_STEPS", 40);  // 0: warp per response only
     const int path = path_choice();
     const int log2T = fused_log2T(out_capacity, n_req);
-    if (n_resp > 0 && (path == kPathFused || (path == kPathAuto && log2T <= kFusedMaxAutoLog2T))) {
+    if (n_resp > 0 && (path == kPathFused || (path == kPathAuto && mean_unit_bytes(out_capacity, n_req) <= kFusedMaxAutoMean))) {
         // single pass: tile map, then one persistent kernel (qb_fused.cuh)
         uint8_t* fsp = tok_scratch + tok_scratch_bytes(out_capacity);
         const TileTables tt = fused_tables(fsp, out_capacity, log2T);
-        CUDA_TRY(cudaMemsetAsync(fsp, 0, fused_scratch_bytes(out_capacity), stream));
+        CUDA_TRY(cudaMemsetAsync(fsp, 0, fused_table_bytes(out_capacity, log2T), stream));
         strip_tile_map_kernel<<<(unsigned)((n_req + 255) / 256), 256, 0, stream>>>(in_off, req_off, n_req, tt);
         LAUNCHED("strip_tile_map_kernel");
         StripFusedParams P;
@@ -994,7 +1010,9 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
         P.g_max_steps = st;
         P.tt = tt;
         P.lane_steps = lane_steps;
-        strip_fused_kernel<<<fused_grid(tt.max_tiles), kThreads, 0, stream>>>(tags->dev, P);
+        void* args[] = {(void*)&tags->dev, (void*)&P};
+        CUDA_TRY(cudaLaunchCooperativeKernel((const void*)strip_fused_kernel, dim3(fused_grid((const void*)strip_fused_kernel, 0, tt.max_tiles)),
+                                             dim3(kThreads), args, 0, stream));
         LAUNCHED("strip_fused_kernel");
         CUDA_TRY(cudaGetLastError());
         return QB200_OK;
@@ -1132,7 +1150,7 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
     cudaStream_t stream = (cudaStream_t)stream_;
     const int path = path_choice();
     const int log2T = fused_log2T(out_capacity, n_streams);
-    const bool fused = n_streams > 0 && (path == kPathFused || (path == kPathAuto && log2T <= kFusedMaxAutoLog2T));
+    const bool fused = n_streams > 0 && (path == kPathFused || (path == kPathAuto && mean_unit_bytes(out_capacity, n_streams) <= kFusedMaxAutoMean));
     if (!fused) {
         const bool tok = path != kPathGeneral && n_streams > 0;
         if (tok && (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams, out_capacity) || !scratch))
@@ -1171,10 +1189,12 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
     uint8_t* fsp = tok_scratch + tok_scratch_bytes(out_capacity) + sid_scratch_bytes(n_chunks);
     P.tt = fused_tables(fsp, out_capacity, log2T);
     P.lane_steps = env_int("QB200_LANE_STEPS", 40);
-    CUDA_TRY(cudaMemsetAsync(fsp, 0, fused_scratch_bytes(out_capacity), stream));
+    CUDA_TRY(cudaMemsetAsync(fsp, 0, fused_table_bytes(out_capacity, log2T), stream));
     stream_tile_map_kernel<<<(unsigned)((n_streams + 255) / 256), 256, 0, stream>>>(chunk_off, stream_off, n_streams, P.tt);
     LAUNCHED("stream_tile_map_kernel");
-    stream_fused_kernel<<<fused_grid(P.tt.max_tiles), kThreads, 0, stream>>>(tags->dev, P);
+    void* args[] = {(void*)&tags->dev, (void*)&P};
+    CUDA_TRY(cudaLaunchCooperativeKernel((const void*)stream_fused_kernel, dim3(fused_grid((const void*)stream_fused_kernel, 1, P.tt.max_tiles)),
+                                         dim3(kThreads), args, 0, stream));
     LAUNCHED("stream_fused_kernel");
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
@@ -1406,6 +1426,17 @@ int qb200_usage_sums_batch(const int64_t* usage, const int64_t* req_off, int64_t
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
 }
+
+#ifdef QB_PHASE_TIMING
+// debug builds only: read and clear the per-phase nanosecond sums of the fused kernels
+int qb200_debug_phases(unsigned long long* out16) {
+    CUDA_TRY(cudaDeviceSynchronize());
+    CUDA_TRY(cudaMemcpyFromSymbol(out16, g_phase_ns, 16 * sizeof(unsigned long long)));
+    unsigned long long z[16] = {0};
+    CUDA_TRY(cudaMemcpyToSymbol(g_phase_ns, z, sizeof(z)));
+    return QB200_OK;
+}
+#endif
 
 int qb200_stream_flush_batch(qb200_stream_state* state, int64_t n_streams, void* stream_) {
     if (n_streams < 0 || (n_streams > 0 && !state)) return fail(QB200_EINVAL, "stream_flush_batch: bad argument");

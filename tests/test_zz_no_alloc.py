@@ -56,6 +56,43 @@ def test_noalloc_matches_allocating_entry_point_twice_in_a_row():
         assert torch.equal(state, exp_state), f"call {call}: carried state differs"
 
 
+def _batch_few_chunks(seed, n_streams, dev):
+    """Many short streams (4 chunks x 64 B each), so that batch sizes near the limit stay small."""
+    from quorum_b200 import synth
+    base = synth.cfg2_base(48, chunks=4, chunk_bytes=64, seed=seed)
+    idx = synth.gather_units(base, n_streams, seed=seed + 1)
+    data = np.ascontiguousarray(base[idx]).reshape(-1)
+    chunk_off = np.arange(0, data.size + 1, 64, dtype=np.int64)
+    stream_off = np.arange(0, n_streams * 4 + 1, 4, dtype=np.int64)
+    t = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+    return t(data), t(chunk_off), t(stream_off)
+
+
+def test_noalloc_at_the_scan_split_and_at_the_limit():
+    """Two more calls in a row on the shared array: 8,193 streams (the first size at which the prefix sum over the streams
+    takes three launches and keeps its partial sums in the array's last KiB) and 65,536 streams (the documented limit, the
+    whole array in use); a small batch in between must not see what the large one left behind."""
+    from quorum_b200 import _lib, batch
+
+    dev = torch.device("cuda", 0)
+    table = batch.tag_table(["think", "reason", "reasoning", "thought", "Thought"])
+    for call, (seed, n_streams) in enumerate([(51, 8193), (52, _lib.NOALLOC_MAX_STREAMS), (53, 77), (54, 8192)]):
+        data, chunk_off, stream_off = _batch_few_chunks(seed, n_streams, dev)
+        n_chunks = chunk_off.numel() - 1
+        exp_out, exp_oco, exp_state = batch.stream_feed_batch(table, data, chunk_off, stream_off, None, flush=True)
+        out = torch.zeros(data.numel() + _lib.HELD_MAX * n_streams + 16, dtype=torch.uint8, device=dev)
+        oco = torch.zeros(n_chunks + 1, dtype=torch.int64, device=dev)
+        state = torch.zeros((n_streams, _lib.STATE_BYTES), dtype=torch.uint8, device=dev)
+        batch.stream_feed_batch_noalloc(table, data, chunk_off, stream_off, None, flush=True, state_out=state,
+                                        out_bytes=out, out_chunk_off=oco)
+        torch.cuda.synchronize()
+        total = int(exp_oco[-1].item())
+        assert total > 0
+        assert torch.equal(oco, exp_oco), f"call {call} ({n_streams} streams): per-chunk offsets differ"
+        assert torch.equal(out[:total], exp_out[:total]), f"call {call} ({n_streams} streams): output bytes differ"
+        assert torch.equal(state, exp_state), f"call {call} ({n_streams} streams): carried state differs"
+
+
 def test_noalloc_rejects_batches_over_its_limit():
     from quorum_b200 import _lib, batch
 

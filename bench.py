@@ -236,11 +236,15 @@ def time_cpu(wl, name, base, cores, sample_units, repeats=1, force_port=False):
                     res = pool.map(_ref_stream_shard, [(s, wl["chunk_bytes"], tags) for s in shards])
                 else:
                     res = pool.map(_ref_resp_shard, [(s, wl["per_request"], tags, synth.SEP_MULTIBYTE) for s in shards])
-                dt = time.perf_counter() - t0
+                wall = time.perf_counter() - t0
                 nbytes = sum(r[0] for r in res)
+                # the workers run side by side, one shard each: the parallel compute time is the slowest worker's own
+                # clock around its loop (shipping the shard to the worker - pickling, pipes - is not the reference's work)
+                dt = max(r[1] for r in res)
                 best = dt if best is None else min(best, dt)
         kind = "reference"
-        how = f"unmodified reference module (CPython {sys.version.split()[0]}), multiprocessing.Pool({cores})"
+        how = (f"unmodified reference module (CPython {sys.version.split()[0]}), multiprocessing.Pool({cores}), slowest worker's "
+               f"compute time (wall clock incl. shipping the shards: {wall:.2f} s)")
     else:
         from concurrent.futures import ThreadPoolExecutor
         from oracle import c_oracle

@@ -6,7 +6,7 @@ import ctypes
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.environ.get("QB200_LIB") or os.path.join(HERE, "libquorum_b200.so")   # QB200_LIB: a debug build (tools/)
+LIB_PATH = os.path.join(HERE, "libquorum_b200.so")
 
 QB200_HIDE, QB200_STREAM_JOIN, QB200_FLUSH, QB200_CHAIN, QB200_SKIP_EMPTY = 1, 2, 4, 8, 16
 HELD_MAX = 23

@@ -244,144 +244,190 @@ __device__ __forceinline__ bool stream_walk_lane(const DevTags& tg, const uint8_
     return true;
 }
 
-// Lane-per-response strip_thinking_tags (same semantics and descriptor as StripRunWalker<false>): liveness of an open tag
-// ("a closer of its class follows", oai_proxy.py:137-139 as restated in SURVEY.md A.1) comes from one backward pass over
-// the response's records that keeps a bit per class; the forward pass is the two-state automaton; `.strip()` looks at
-// the two ends of the run list.  Returns false (nothing written) when the response needs the warp walker: 2 GiB and
-// more, overflowed record slots, more than 64 records, more than kDescRuns kept runs.
+// Kept runs of the units that have more than a descriptor holds (kDescRuns): a bump-allocated pool in the call's scratch.
+// The count kernel writes a unit's runs once, the copy kernel reads them back - no second walk over the records.  `top`
+// is zeroed by the tokenizer kernel of the call; a unit that does not get its slots (pool exhausted) falls back to the
+// warp walkers, which settle any number of runs 32 at a time.
+struct RunPool {
+    int2* runs = nullptr;
+    unsigned long long* top = nullptr;
+    int64_t cap = 0;  // slots
+};
+constexpr int kLaneCls = 16;       // backreference classes a lane can track (the default 5-tag table has 9)
+constexpr uint32_t kDescPooled = 8;  // UnitDesc.flags: runs live in the pool at index run_s[0] | run_s[1] << 32
+
+// One lane visits the records of the steps [s_first, s_last] in position order: f(r, x) with x = unit position of the
+// '<' (records of other units in a shared step have x < 0 or end beyond n: the callee filters).  Eight steps at a time:
+// their record counts are fetched together and the record lines of the steps that have any are pulled towards the SM
+// before the first one is read (a lane has nothing else to hide a miss behind).  Returns false on an overflowed step.
+template <class F>
+__device__ __forceinline__ bool for_each_record(const TokSrc& ts, int64_t s_first, int64_t s_last, int64_t ustart, F&& f) {
+    // (measured on cfg5: a two-batch-deep software pipeline of the count loads plus one flattened loop over the records of
+    // a batch, as the stream walker has, made this slower - 1.09 vs 0.61 ms - so the loops stay nested)
+    for (int64_t s0 = s_first; s0 <= s_last; s0 += 8) {
+        unsigned long long cpack = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            if (s0 + i <= s_last) cpack |= (unsigned long long)ts.cnt[s0 + i] << (8 * i);
+        if (cpack == 0) continue;
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            if ((cpack >> (8 * i)) & 0xFF) asm volatile("prefetch.global.L1 [%0];" ::"l"(ts.rec + (s0 + i) * kRecPerStep));
+        for (int i = 0; i < 8; i++) {
+            const int cnt = (int)((cpack >> (8 * i)) & 0xFF);
+            if (cnt == 0) continue;
+            if (cnt == kRecOverflow) return false;
+            const int64_t sj = s0 + i;
+            const uint32_t* rp = ts.rec + sj * kRecPerStep;
+            const int sb = (int)((sj << 10) - ustart);
+            for (int q = 0; q < cnt; q++) {
+                const uint32_t r = rp[q];
+                f(r, sb + (int)(r & 1023));
+            }
+        }
+    }
+    return true;
+}
+
+// Lane-per-response strip_thinking_tags (same semantics as StripRunWalker<false>): liveness of an open tag ("a closer of
+// its class follows", oai_proxy.py:137-139 as restated in SURVEY.md A.1) comes from one pass over the response's records
+// that keeps the LAST closer position of every class (lc[], one int per class and thread in shared memory, strided by the
+// block size) and counts the open tags; a second pass is the two-state automaton; `.strip()` looks at the two ends of
+// the run list.  Any number of records; a response that can have more than kDescRuns kept runs (runs <= open tags + 1)
+// takes that many slots of the run pool before the second pass and writes its runs there, otherwise they stay in
+// registers and go to the descriptor.  Returns false (nothing written) when the response needs the warp walker: 2 GiB
+// and more, overflowed record slots, more classes than kLaneCls, pool exhausted.
 __device__ __forceinline__ bool strip_walk_lane(const DevTags& tg, const uint8_t* buf, int64_t ustart, int64_t n64, const TokSrc& ts,
-                                                UnitDesc* dsc, int64_t& kept_len) {
+                                                UnitDesc* dsc, int64_t& kept_len, int* lc, int lc_stride, const RunPool& pool) {
     kept_len = 0;
     if (n64 <= 0) {  // empty response: nothing to walk, nothing to copy
         dsc->nruns = 0;
+        dsc->flags = 0;
         return true;
     }
-    if (n64 >= (int64_t)1 << 31) return false;
+    if (n64 >= (int64_t)1 << 31 || tg.ncls > kLaneCls) return false;
     const int n = (int)n64;
     const PtrAcc T{buf + ustart};
     const int64_t s_first = ustart >> 10, s_last = (ustart + n - 1) >> 10;
-    int tot = 0;
-    for (int64_t sj = s_first; sj <= s_last; sj++) {
-        const int cnt = ts.cnt[sj];
-        if (cnt == kRecOverflow) return false;
-        tot += cnt;
+    // pass A: last closer of every class, number of open tags
+    for (int c = 0; c < tg.ncls; c++) lc[c * lc_stride] = 0;
+    int n_open = 0;
+    if (!for_each_record(ts, s_first, s_last, ustart, [&](uint32_t r, int x) {
+            const int kind = (r >> 17) & 3;
+            if (kind == 2 || x < 0 || x + (int)((r >> 10) & 127) > n) return;
+            if (kind == 1) lc[((r >> 19) & 127) * lc_stride] = x + 1;
+            else n_open++;
+        }))
+        return false;
+    const bool pooled = n_open + 1 > kDescRuns;
+    int2* pr = nullptr;
+    unsigned long long at = 0;
+    if (pooled) {
+        if (!pool.runs) return false;
+        at = atomicAdd(pool.top, (unsigned long long)(n_open + 1));
+        if (at + (unsigned long long)(n_open + 1) > (unsigned long long)pool.cap) return false;
+        pr = pool.runs + at;
     }
-    if (tot > 64) return false;
-    // backward: which open tags are live?  bit i of `live` <-> the i-th record of the response (all kinds counted)
-    unsigned long long live = 0, seen0 = 0, seen1 = 0;  // seen: classes that have a closer further on
-    if (tot > 0) {
-        int idx = tot;
-        for (int64_t sj = s_last; sj >= s_first; sj--) {
-            const int cnt = ts.cnt[sj];
-            const uint32_t* rp = ts.rec + sj * kRecPerStep;
-            const int sb = (int)((sj << 10) - ustart);
-            for (int q = cnt - 1; q >= 0; q--) {
-                idx--;
-                const uint32_t r = rp[q];
-                const int kind = (r >> 17) & 3;
-                const int x = sb + (int)(r & 1023);
-                const int tend = x + (int)((r >> 10) & 127);
-                if (kind == 2 || x < 0 || tend > n) continue;
-                const int cls = (r >> 19) & 127;
-                const unsigned long long bit = 1ull << (cls & 63);
-                if (kind == 1) {
-                    if (cls < 64) seen0 |= bit;
-                    else seen1 |= bit;
-                } else if ((cls < 64 ? seen0 : seen1) & bit) {
-                    live |= 1ull << idx;
-                }
-            }
-        }
-    }
-    // forward: the automaton over the tags in position order
+    // pass B: the automaton over the tags in position order
     int rs[kDescRuns], re[kDescRuns];
     int nruns = 0, state = -1, seg_start = 0;
-    if (live) {  // no live open tag: the whole response is one run
-        int idx = 0;
-        for (int64_t sj = s_first; sj <= s_last; sj++) {
-            const int cnt = ts.cnt[sj];
-            const uint32_t* rp = ts.rec + sj * kRecPerStep;
-            const int sb = (int)((sj << 10) - ustart);
-            for (int q = 0; q < cnt; q++, idx++) {
-                const uint32_t r = rp[q];
-                const int kind = (r >> 17) & 3;
-                const int x = sb + (int)(r & 1023);
-                const int tend = x + (int)((r >> 10) & 127);
-                if (kind == 2 || x < 0 || tend > n) continue;
-                const int cls = (r >> 19) & 127;
-                if (state < 0) {
-                    if (kind == 0 && ((live >> idx) & 1ull)) {
-                        if (x > seg_start) {
-                            if (nruns < kDescRuns) {
-                                rs[nruns] = seg_start;
-                                re[nruns] = x;
-                            }
-                            nruns++;
-                        }
-                        state = cls;
-                    }
-                } else if (kind == 1 && cls == state) {
-                    seg_start = tend;
-                    state = -1;
-                }
-            }
-        }
-    }
-    if (n > seg_start) {
-        if (nruns < kDescRuns) {
-            rs[nruns] = seg_start;
-            re[nruns] = n;
+    auto emit = [&](int s, int e) {
+        if (pooled) {
+            pr[nruns] = make_int2(s, e);
+        } else {
+            rs[nruns] = s;
+            re[nruns] = e;
         }
         nruns++;
-    }
-    if (nruns > kDescRuns) return false;
+    };
+    if (n_open > 0)
+        for_each_record(ts, s_first, s_last, ustart, [&](uint32_t r, int x) {
+            const int kind = (r >> 17) & 3;
+            const int tend = x + (int)((r >> 10) & 127);
+            if (kind == 2 || x < 0 || tend > n) return;
+            const int cls = (r >> 19) & 127;
+            if (state < 0) {
+                if (kind == 0 && lc[cls * lc_stride] > x) {  // live: a closer of its class starts later
+                    if (x > seg_start) emit(seg_start, x);
+                    state = cls;
+                }
+            } else if (kind == 1 && cls == state) {
+                seg_start = tend;
+                state = -1;
+            }
+        });
+    if (n > seg_start) emit(seg_start, n);
     // .strip(): white space goes from the front of the first run that keeps anything and from the back of the last
+    auto get = [&](int i) -> int2 {
+        return pooled ? pr[i] : make_int2(rs[i], re[i]);
+    };
+    auto put = [&](int i, int s, int e) {
+        if (pooled) {
+            pr[i] = make_int2(s, e);
+        } else {
+            rs[i] = s;
+            re[i] = e;
+        }
+    };
     int lead = -1;
     for (int i = 0; i < nruns && lead < 0; i++) {
+        const int2 run = get(i);
         int f = -1;
-        for (int x = rs[i]; x < re[i]; x++)
+        for (int x = run.x; x < run.y; x++)
             if (!is_white_byte(T, x, n)) {
                 f = x;
                 break;
             }
         if (f >= 0) {
-            rs[i] = f;
+            put(i, f, run.y);
             lead = i;
         } else {
-            re[i] = rs[i];  // all white
+            put(i, run.x, run.x);  // all white
         }
     }
     if (lead >= 0) {
         for (int i = nruns - 1; i >= lead; i--) {
+            const int2 run = get(i);
             int l = -1;
-            for (int x = re[i] - 1; x >= rs[i]; x--)
+            for (int x = run.y - 1; x >= run.x; x--)
                 if (!is_white_byte(T, x, n)) {
                     l = x;
                     break;
                 }
             if (l >= 0) {
-                re[i] = l + 1;
+                put(i, run.x, l + 1);
                 break;
             }
-            re[i] = rs[i];
+            put(i, run.x, run.x);
         }
     }
-    int kl = 0;
-    for (int i = 0; i < nruns; i++) kl += re[i] - rs[i];
+    int64_t kl = 0;
+    if (pooled) {
+        for (int i = 0; i < nruns; i++) {
+            const int2 run = pr[i];
+            kl += run.y - run.x;
+        }
+    } else {
+        for (int i = 0; i < nruns; i++) kl += re[i] - rs[i];
+    }
     kept_len = kl;
     UnitDesc& d = *dsc;
     d.nruns = nruns;
-    d.total = kl;
+    d.total = (int32_t)kl;
     d.held_kept = 0;
     d.depth = 0;
     d.last_tok_end = -1;
     d.rlast = n;
-    d.flags = 0;
     d.held_len = 0;
+    d.flags = pooled ? kDescPooled : 0;
 #pragma unroll
     for (int i = 0; i < kDescRuns; i++) {
-        d.run_s[i] = i < nruns ? rs[i] : 0;
-        d.run_e[i] = i < nruns ? re[i] : 0;
+        d.run_s[i] = (!pooled && i < nruns) ? rs[i] : 0;
+        d.run_e[i] = (!pooled && i < nruns) ? re[i] : 0;
+    }
+    if (pooled) {
+        d.run_s[0] = (int32_t)(uint32_t)(at & 0xffffffffull);
+        d.run_s[1] = (int32_t)(uint32_t)(at >> 32);
     }
     return true;
 }

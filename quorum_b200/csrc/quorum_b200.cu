@@ -1,8 +1,6 @@
 // quorum_b200 — kernels + C ABI (include/quorum_b200.h).  sm_100a only; no CPU fallback.
 //
-// Default path (QB200_PATH=fused, qb_fused.cuh): one persistent kernel per call, tile by tile:
-//   tokenise -> walk (lane per unit) -> scan + look-back -> offsets -> copy, the text read from HBM once.
-// Token path (QB200_PATH=token; also what units / shapes the fused kernel is not chosen for use), DESIGN.md section 5.2:
+// Default path (QB200_PATH=token), see DESIGN.md section 5.1:
 //   stream_feed :  tokenize (one record per '<')  ->  count (lane per stream: automaton over the records, descriptor,
 //                  carried state, prefix sum over the streams by look-back)  ->  offsets (thread per feed boundary)
 //                  ->  finish (warp per stream: kept runs to their final place)
@@ -98,6 +96,24 @@ __device__ __noinline__ bool strip_count_wide(const DevTags& tg, const uint8_t* 
     *kept_len = w.kept_len;
     return !w.overflow;
 }
+// the record-driven warp walker of one response, out of line for the same reason (the lane walker is the common case)
+__device__ __noinline__ StripResult strip_count_warp(const DevTags& tg, const uint8_t* in, int64_t total, int64_t a, int64_t n,
+                                                     unsigned long long* lc, int lane, TokSrc ts, UnitDesc* desc) {
+    StripResult res;
+    res.first_pos = 0;
+    StripRunWalker<false> w(tg, in, total, a, n, lc, lane, ts);
+    w.desc = desc;
+    if (n == 0 && lane == 0) desc->nruns = 0;  // empty response: nothing to walk, nothing to copy
+    w.run();
+    res.kept_len = w.kept_len;
+    bool slow = w.overflow;
+    if (w.many) slow = !strip_count_wide(tg, in, total, a, n, lc, lane, ts, desc, &res.kept_len);
+    if (slow) {
+        res = strip_count_slow(tg, in, total, a, n, lc, lane);
+        if (lane == 0) desc->nruns = -1;  // redone from the bytes by the copy kernel
+    }
+    return res;
+}
 __device__ __noinline__ StreamResult stream_count_slow(const DevTags& tg, const uint8_t* bytes, int64_t total, const int64_t* co,
                                                        int64_t m, int lane, uint32_t flags, const StreamState* st_in) {
     StreamWalker<false> w(tg, bytes, total, co, m, lane, flags);
@@ -140,8 +156,9 @@ __device__ __forceinline__ void prefetch_unit_meta(const TokSrc& ts, const uint8
 __global__ void __launch_bounds__(kThreads, 4)
 strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
                    int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first, TokSrc ts,
-                   UnitDesc* __restrict__ desc, int lane_steps) {
+                   UnitDesc* __restrict__ desc, int lane_steps, RunPool pool) {
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
+    __shared__ int s_lc[kLaneCls][kThreads];  // lane walker: last closer per class, one column per thread
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
     const int64_t ngroups = (n_resp + 31) >> 5;
@@ -155,7 +172,7 @@ strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
         if (have) {
             a = in_off[r];
             b = in_off[r + 1];
-            if (ts.cnt && (b <= a || ((b - 1) >> 10) - (a >> 10) < lane_steps)) done = strip_walk_lane(tg, in, a, b - a, ts, desc + r, kl);
+            if (ts.cnt && (b <= a || ((b - 1) >> 10) - (a >> 10) < lane_steps)) done = strip_walk_lane(tg, in, a, b - a, ts, desc + r, kl, &s_lc[0][threadIdx.x], kThreads, pool);
         }
         __syncwarp();
         unsigned todo = __ballot_sync(kFull, have && !done);
@@ -165,21 +182,8 @@ strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
             const int64_t rj = (g << 5) + j;
             const int64_t aj = __shfl_sync(kFull, a, j), bj = __shfl_sync(kFull, b, j);
             StripResult res;
-            bool slow = ts.cnt == nullptr;
-            if (!slow) {
-                StripRunWalker<false> w(tg, in, total, aj, bj - aj, lastclose[wib], lane, ts);
-                w.desc = desc + rj;
-                if (bj == aj && lane == 0) desc[rj].nruns = 0;  // empty response: nothing to walk, nothing to copy
-                w.run();
-                res.kept_len = w.kept_len;
-                res.first_pos = 0;
-                slow = w.overflow;
-                if (w.many) slow = !strip_count_wide(tg, in, total, aj, bj - aj, lastclose[wib], lane, ts, desc + rj, &res.kept_len);
-            }
-            if (slow) {
-                res = strip_count_slow(tg, in, total, aj, bj - aj, lastclose[wib], lane);
-                if (desc && lane == 0) desc[rj].nruns = -1;  // redone from the bytes by the copy kernel
-            }
+            if (ts.cnt) res = strip_count_warp(tg, in, total, aj, bj - aj, lastclose[wib], lane, ts, desc + rj);
+            else res = strip_count_slow(tg, in, total, aj, bj - aj, lastclose[wib], lane);
             if (lane == j) {
                 kl = res.kept_len;
                 fp = res.first_pos;
@@ -388,13 +392,43 @@ __device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, con
     }
 }
 
+// The same for a unit whose runs live in the pool (more than kDescRuns): 32 runs at a time, one per lane for the offsets,
+// then run by run - long runs by the whole warp with 16-byte stores, short ones as lane-strided bytes (coalesced).
+__device__ __forceinline__ void gather_pooled(const int2* __restrict__ runs, int nruns, const uint8_t* src, uint8_t* dst,
+                                              const uint8_t* src_hi, int lane) {
+    int done = 0;
+    for (int base = 0; base < nruns; base += 32) {
+        const int i = base + lane;
+        int2 run = make_int2(0, 0);
+        if (i < nruns) run = runs[i];
+        const int len = run.y - run.x;
+        int incl = len;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(kFull, incl, d);
+            if (lane >= d) incl += t;
+        }
+        const int off = done + incl - len;
+        const int m = min(32, nruns - base);
+        for (int j = 0; j < m; j++) {
+            const int s_j = __shfl_sync(kFull, run.x, j), l_j = __shfl_sync(kFull, len, j), o_j = __shfl_sync(kFull, off, j);
+            if (l_j >= 128) {
+                warp_copy_fast(dst + o_j, src + s_j, l_j, src_hi, lane);
+            } else {
+                for (int k = lane; k < l_j; k += 32) dst[o_j + k] = src[s_j + k];
+            }
+        }
+        done += __shfl_sync(kFull, incl, 31);
+    }
+}
+
 // strip + concat, last kernel: every response's kept runs (and the separator in front of it) go to their final place.
 __global__ void __launch_bounds__(kThreads, 5)
 strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
                   int64_t n_resp, const int64_t* __restrict__ klen, const int64_t* __restrict__ first,
                   const int64_t* __restrict__ dst, int hide, const uint8_t* __restrict__ sep, int32_t sep_len,
                   uint8_t* __restrict__ out, int64_t* __restrict__ resp_out_len, const UnitDesc* __restrict__ desc,
-                  TokSrc ts) {
+                  TokSrc ts, RunPool pool) {
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
@@ -414,7 +448,10 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
             warp_copy<true>(out + d, in + a, b - a, in + total, lane);
         } else if (kl > 0) {
             const int nr = desc ? desc[r].nruns : -1;
-            if (nr >= 0) {
+            if (nr >= 0 && (desc[r].flags & kDescPooled)) {
+                const unsigned long long at = (unsigned long long)(uint32_t)desc[r].run_s[0] | ((unsigned long long)(uint32_t)desc[r].run_s[1] << 32);
+                gather_pooled(pool.runs + at, nr, in + a, out + d, in + total, lane);
+            } else if (nr >= 0) {
                 gather_unit<0>(desc + r, in + a, out + d, in + total, lane);
             } else if (nr == -2) {  // 9..32 kept runs: walk the records again and copy from the lanes
                 strip_copy_wide(tg, in, total, a, b - a, lastclose[wib], lane, ts, kl, out + d);
@@ -690,8 +727,6 @@ __global__ void stream_flush_kernel(StreamState* st, int64_t n) {
 
 __global__ void set_i64_kernel(int64_t* p, int64_t v) { *p = v; }
 
-#include "qb_fused.cuh"
-
 // ---------------------------------------------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------------------------------------------
@@ -806,53 +841,19 @@ int qb200_tags_create(const uint8_t* names, const int32_t* name_off, int32_t n_t
 
 void qb200_tags_destroy(qb200_tags* tags) { delete tags; }
 
-// QB200_PATH selects the implementation: "fused" = single-pass tile kernels (qb_fused.cuh), "token" = tokenizer pass +
-// record-driven kernels, "general" = walkers that rescan the bytes.  Unset: fused, except for batches whose units are so
-// large that a tile would not stay in L2 between its two touches (then the token path, which is what the fused kernel
-// degenerates to anyway, minus its serial per-tile chain).
+// QB200_PATH selects the implementation (default "token"): "token" = tokenizer pass + record-driven kernels,
+// "general" = walkers that rescan the bytes.
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-enum { kPathGeneral = 0, kPathToken = 2, kPathFused = 3, kPathAuto = 4 };
+enum { kPathGeneral = 0, kPathToken = 2 };
 static int path_choice() {
     const char* e = getenv("QB200_PATH");
     if (e && strcmp(e, "general") == 0) return kPathGeneral;
-    if (e && strcmp(e, "token") == 0) return kPathToken;
-    if (e && strcmp(e, "fused") == 0) return kPathFused;
-    return kPathAuto;
+    return kPathToken;
 }
 static int env_int(const char* name, int dflt) {
     const char* e = getenv(name);
     return e ? atoi(e) : dflt;
-}
-
-// Window size of the fused kernels: 16 KiB (what a warp's shared record slice covers), 8 KiB when the units are small
-// (more units per tile than that is no gain, and a shorter tile has a shorter chain).  Larger units simply span several
-// windows; their records then go to the global arrays.
-constexpr int64_t kFusedMaxAutoMean = 65536;  // auto path choice: mean unit size up to 64 KiB goes to the fused kernels
-static int64_t mean_unit_bytes(int64_t byte_bound, int64_t n_units) { return n_units > 0 ? byte_bound / n_units : 0; }
-static int fused_log2T(int64_t byte_bound, int64_t n_units) {
-    if (const int v = env_int("QB200_FUSED_LOG2T", 0)) return v < kFusedMinLog2T ? kFusedMinLog2T : (v > 30 ? 30 : v);
-    return mean_unit_bytes(byte_bound, n_units) >= 12288 ? 14 : 13;
-}
-static int64_t fused_max_tiles(int64_t byte_bound, int log2T) { return ((byte_bound < 0 ? 0 : byte_bound) >> log2T) + 2; }
-// per tile: its record (64 B) and its look-back word; per group of 32 tiles: a look-back word.  Sized for the smallest
-// window; a call lays the tables out for its own window size and clears only that part.
-static size_t fused_table_bytes(int64_t byte_bound, int log2T) {
-    const int64_t mt = fused_max_tiles(byte_bound, log2T), mg = mt / 32 + 2;
-    return align256((size_t)mt * 72 + (size_t)mg * 8 + 64);
-}
-static size_t fused_scratch_bytes(int64_t byte_bound) { return fused_table_bytes(byte_bound, kFusedMinLog2T); }
-static TileTables fused_tables(uint8_t* p, int64_t byte_bound, int log2T) {
-    const int64_t mt = fused_max_tiles(byte_bound, log2T);
-    TileTables tt;
-    tt.rec = (TileRec*)p;
-    p += (size_t)mt * 64;
-    tt.lb.state = (unsigned long long*)p;
-    p += (size_t)mt * 8;
-    tt.lb.gstate = (unsigned long long*)p;
-    tt.max_tiles = mt;
-    tt.log2T = log2T;
-    return tt;
 }
 
 static int64_t steps_for(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte_bound) / 1024 + 2; }
@@ -889,9 +890,14 @@ static size_t strip_general_scratch_bytes(int64_t n_resp, int64_t n_req) {
 static size_t desc_scratch_bytes(int64_t n_units) { return align256((size_t)(n_units < 0 ? 0 : n_units) * sizeof(UnitDesc) + 96); }
 static size_t stream_desc_scratch_bytes(int64_t n_units) { return align256((size_t)(n_units < 0 ? 0 : n_units) * sizeof(StreamDesc) + 96); }
 
+// run pool: one 8-byte slot per 128 bytes of input bound (a kept run plus the block it follows is rarely shorter), plus the
+// allocation counter; units that do not get their slots fall back to the warp walkers
+static int64_t pool_slots(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte_bound) / 128 + 64; }
+static size_t pool_scratch_bytes(int64_t byte_bound) { return align256((size_t)pool_slots(byte_bound) * 8) + 256; }
+
 size_t qb200_strip_concat_scratch_bytes(int64_t n_resp, int64_t n_req, int64_t out_capacity) {
     return strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp) + tok_scratch_bytes(out_capacity) +
-           fused_scratch_bytes(out_capacity) + 256;
+           pool_scratch_bytes(out_capacity) + 256;
 }
 
 // per-device facts, cached per device ordinal (one process may drive several GPUs)
@@ -905,26 +911,6 @@ static int sm_count() {
         cache[dev].store(n, std::memory_order_relaxed);
     }
     return n;
-}
-
-// Grid of the fused kernels: every CTA must be resident at once (tiles are dealt statically and a tile waits, in its
-// look-back, for tiles that other warps hold), so the size comes from the occupancy calculator and the launch is a
-// cooperative one, which fails instead of deadlocking if the grid would not fit.  Cached per device and kernel.
-static int fused_grid(const void* kernel, int which, int64_t max_tiles) {
-    static std::atomic<int> cache[64][2];
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
-    int per_sm = cache[dev][which].load(std::memory_order_relaxed);
-    if (!per_sm) {
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
-        cache[dev][which].store(per_sm, std::memory_order_relaxed);
-    }
-    int64_t g = (int64_t)per_sm * sm_count();
-    if (const int v = env_int("QB200_GRID_CAP", 0)) g = v < g ? v : g;  // test knob: a small grid makes every warp loop over many tiles
-    const int64_t need = (max_tiles + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    if (g > need) g = need;
-    if (g < 1) g = 1;
-    return (int)g;
 }
 
 static int grid_for(int64_t units) {
@@ -976,52 +962,19 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     TokSrc ts;
     UnitDesc* desc = (UnitDesc*)((uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req));
     uint8_t* tok_scratch = (uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp);
-    const int lane_steps = env_int("QB200_LANE_STEPS", 40);  // 0: warp per response only
+    const int lane_steps = env_int("QB200_LANE_STEPS", 72);  // 0: warp per response only
     const int path = path_choice();
-    const int log2T = fused_log2T(out_capacity, n_req);
-    if (n_resp > 0 && (path == kPathFused || (path == kPathAuto && mean_unit_bytes(out_capacity, n_req) <= kFusedMaxAutoMean))) {
-        // single pass: tile map, then one persistent kernel (qb_fused.cuh)
-        uint8_t* fsp = tok_scratch + tok_scratch_bytes(out_capacity);
-        const TileTables tt = fused_tables(fsp, out_capacity, log2T);
-        CUDA_TRY(cudaMemsetAsync(fsp, 0, fused_table_bytes(out_capacity, log2T), stream));
-        strip_tile_map_kernel<<<(unsigned)((n_req + 255) / 256), 256, 0, stream>>>(in_off, req_off, n_req, tt);
-        LAUNCHED("strip_tile_map_kernel");
-        StripFusedParams P;
-        P.in = in_bytes;
-        P.in_off = in_off;
-        P.n_resp = n_resp;
-        P.req_off = req_off;
-        P.n_req = n_req;
-        P.sep = sep;
-        P.sep_len = sep_len;
-        P.hide = hide;
-        P.stream_join = sj;
-        P.chain = chain ? 1 : 0;
-        P.out = out_bytes;
-        P.out_off = out_off;
-        P.resp_out_len = resp_out_len;
-        P.klen = klen;
-        P.first = first;
-        P.dst = dst;
-        P.desc = desc;
-        const int64_t st = steps_for(out_capacity);
-        P.g_cnt = tok_scratch;
-        P.g_rec = (uint32_t*)(tok_scratch + align256((size_t)st));
-        P.g_max_steps = st;
-        P.tt = tt;
-        P.lane_steps = lane_steps;
-        void* args[] = {(void*)&tags->dev, (void*)&P};
-        CUDA_TRY(cudaLaunchCooperativeKernel((const void*)strip_fused_kernel, dim3(fused_grid((const void*)strip_fused_kernel, 0, tt.max_tiles)),
-                                             dim3(kThreads), args, 0, stream));
-        LAUNCHED("strip_fused_kernel");
-        CUDA_TRY(cudaGetLastError());
-        return QB200_OK;
+    RunPool pool;
+    if (hide && n_resp > 0 && path != kPathGeneral) {
+        uint8_t* pp = tok_scratch + tok_scratch_bytes(out_capacity);
+        pool.top = (unsigned long long*)pp;
+        pool.runs = (int2*)(pp + 256);
+        pool.cap = pool_slots(out_capacity);
+        ts = launch_tokenizer(tags->dev, in_bytes, in_off, nullptr, n_resp, out_capacity, tok_scratch, stream, pool.top, 1);
     }
-    if (hide && n_resp > 0 && path != kPathGeneral)
-        ts = launch_tokenizer(tags->dev, in_bytes, in_off, nullptr, n_resp, out_capacity, tok_scratch, stream);
     if (hide && n_resp > 0) {
         strip_count_kernel<<<grid_for((n_resp + 31) / 32), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts,
-                                                                                 ts.cnt ? desc : nullptr, lane_steps);
+                                                                                 ts.cnt ? desc : nullptr, lane_steps, pool);
         LAUNCHED("strip_count_kernel");
     }
     const int tb = 256;
@@ -1035,7 +988,7 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     if (n_resp > 0) {
         strip_copy_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, dst,
                                                                     hide, sep, sep_len, out_bytes, resp_out_len,
-                                                                    (hide && ts.cnt) ? desc : nullptr, ts);
+                                                                    (hide && ts.cnt) ? desc : nullptr, ts, pool);
         LAUNCHED("strip_copy_kernel");
     }
     CUDA_TRY(cudaGetLastError());
@@ -1051,7 +1004,7 @@ static size_t sid_scratch_bytes(int64_t n_chunks) { return align256((size_t)((n_
 
 size_t qb200_stream_feed_scratch_bytes(int64_t n_chunks, int64_t n_streams, int64_t out_capacity) {
     return stream_general_scratch_bytes(n_streams) + stream_desc_scratch_bytes(n_streams) + tok_scratch_bytes(out_capacity) +
-           sid_scratch_bytes(n_chunks) + fused_scratch_bytes(out_capacity) + 256;
+           sid_scratch_bytes(n_chunks) + 256;
 }
 
 static int stream_feed_check(const qb200_tags* tags, const uint8_t* chunk_bytes, const int64_t* chunk_off, int64_t n_chunks,
@@ -1148,56 +1101,11 @@ int qb200_stream_feed_batch(const qb200_tags* tags, const uint8_t* chunk_bytes, 
                             qb200_stream_state* state_out, uint32_t flags, uint8_t* out_bytes, int64_t out_capacity,
                             int64_t* out_chunk_off, void* scratch, size_t scratch_bytes, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
-    const int path = path_choice();
-    const int log2T = fused_log2T(out_capacity, n_streams);
-    const bool fused = n_streams > 0 && (path == kPathFused || (path == kPathAuto && mean_unit_bytes(out_capacity, n_streams) <= kFusedMaxAutoMean));
-    if (!fused) {
-        const bool tok = path != kPathGeneral && n_streams > 0;
-        if (tok && (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams, out_capacity) || !scratch))
-            return fail(QB200_ESCRATCH, "stream_feed_batch: scratch too small (see qb200_stream_feed_scratch_bytes)");
-        return stream_feed_general(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, state_in, state_out, flags,
-                                   out_bytes, out_capacity, out_chunk_off, scratch, scratch_bytes, stream, tok);
-    }
-    int rc = stream_feed_check(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, out_bytes, out_capacity,
-                               out_chunk_off);
-    if (rc != QB200_OK) return rc;
-    if (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams, out_capacity) || !scratch)
+    const bool tok = path_choice() != kPathGeneral && n_streams > 0;
+    if (tok && (scratch_bytes < qb200_stream_feed_scratch_bytes(n_chunks, n_streams, out_capacity) || !scratch))
         return fail(QB200_ESCRATCH, "stream_feed_batch: scratch too small (see qb200_stream_feed_scratch_bytes)");
-    // single pass: tile map, then one persistent kernel (qb_fused.cuh).  scratch: totals (unused) | bases | ... | descriptors |
-    // records | stream map (unused) | tile tables
-    uint8_t* sp = (uint8_t*)scratch;
-    StreamFusedParams P;
-    P.bytes = chunk_bytes;
-    P.chunk_off = chunk_off;
-    P.n_chunks = n_chunks;
-    P.stream_off = stream_off;
-    P.n_streams = n_streams;
-    P.st_in = reinterpret_cast<const StreamState*>(state_in);
-    P.st_out = reinterpret_cast<StreamState*>(state_out);
-    P.flags = flags;
-    P.chain = (flags & QB200_CHAIN) ? 1 : 0;
-    P.out = out_bytes;
-    P.out_chunk_off = out_chunk_off;
-    P.bases = (int64_t*)(sp + align256((size_t)(n_streams + 2) * 8));
-    uint8_t* tsp = sp + stream_general_scratch_bytes(n_streams);
-    P.desc = (StreamDesc*)tsp;
-    uint8_t* tok_scratch = tsp + stream_desc_scratch_bytes(n_streams);
-    const int64_t st = steps_for(out_capacity);
-    P.g_cnt = tok_scratch;
-    P.g_rec = (uint32_t*)(tok_scratch + align256((size_t)st));
-    P.g_max_steps = st;
-    uint8_t* fsp = tok_scratch + tok_scratch_bytes(out_capacity) + sid_scratch_bytes(n_chunks);
-    P.tt = fused_tables(fsp, out_capacity, log2T);
-    P.lane_steps = env_int("QB200_LANE_STEPS", 40);
-    CUDA_TRY(cudaMemsetAsync(fsp, 0, fused_table_bytes(out_capacity, log2T), stream));
-    stream_tile_map_kernel<<<(unsigned)((n_streams + 255) / 256), 256, 0, stream>>>(chunk_off, stream_off, n_streams, P.tt);
-    LAUNCHED("stream_tile_map_kernel");
-    void* args[] = {(void*)&tags->dev, (void*)&P};
-    CUDA_TRY(cudaLaunchCooperativeKernel((const void*)stream_fused_kernel, dim3(fused_grid((const void*)stream_fused_kernel, 1, P.tt.max_tiles)),
-                                         dim3(kThreads), args, 0, stream));
-    LAUNCHED("stream_fused_kernel");
-    CUDA_TRY(cudaGetLastError());
-    return QB200_OK;
+    return stream_feed_general(tags, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, state_in, state_out, flags,
+                               out_bytes, out_capacity, out_chunk_off, scratch, scratch_bytes, stream, tok);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -1426,17 +1334,6 @@ int qb200_usage_sums_batch(const int64_t* usage, const int64_t* req_off, int64_t
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
 }
-
-#ifdef QB_PHASE_TIMING
-// debug builds only: read and clear the per-phase nanosecond sums of the fused kernels
-int qb200_debug_phases(unsigned long long* out16) {
-    CUDA_TRY(cudaDeviceSynchronize());
-    CUDA_TRY(cudaMemcpyFromSymbol(out16, g_phase_ns, 16 * sizeof(unsigned long long)));
-    unsigned long long z[16] = {0};
-    CUDA_TRY(cudaMemcpyToSymbol(g_phase_ns, z, sizeof(z)));
-    return QB200_OK;
-}
-#endif
 
 int qb200_stream_flush_batch(qb200_stream_state* state, int64_t n_streams, void* stream_) {
     if (n_streams < 0 || (n_streams > 0 && !state)) return fail(QB200_EINVAL, "stream_flush_batch: bad argument");

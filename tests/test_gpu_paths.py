@@ -1,6 +1,6 @@
-"""The three implementations behind the C ABI must agree bit for bit: the fused single-pass tile kernels (default,
-QB200_PATH=fused), the record-driven multi-kernel pipeline (QB200_PATH=token) and the byte-rescanning walkers
-(QB200_PATH=general, also what the other two fall back to for units that do not fit their tables).  Also: full BASELINE.json sizes with sampled oracle checks
+"""The two implementations behind the C ABI must agree bit for bit: the record-driven multi-kernel pipeline (default,
+QB200_PATH=token) and the byte-rescanning walkers (QB200_PATH=general, also what the other falls back to for units that do
+not fit its tables).  Also: full BASELINE.json sizes with sampled oracle checks
 and size-independent properties."""
 import os
 
@@ -38,24 +38,15 @@ def _stream_all_paths(qb, tags, data, chunk_off, stream_off, flush):
     dev = torch.device("cuda", 0)
     table = qb.batch.tag_table(tags)
     res = {}
-    old_t = os.environ.pop("QB200_FUSED_LOG2T", None)
-    try:
-        for path in ("token", "fused", "fused17", "general"):   # fused17: 128 KiB windows (tiles of many units)
-            os.environ["QB200_PATH"] = path[:5]
-            if path == "fused17":
-                os.environ["QB200_FUSED_LOG2T"] = "17"
-            out, oco, st = qb.batch.stream_feed_batch(table, _t(data, dev), _t(chunk_off, dev), _t(stream_off, dev), None,
-                                                      flush=flush)
-            torch.cuda.synchronize()
-            n = int(oco[-1].item())
-            res[path] = (out[:n].cpu().numpy(), oco.cpu().numpy(), st.cpu().numpy())
-    finally:
-        os.environ.pop("QB200_FUSED_LOG2T", None)
-        if old_t is not None:
-            os.environ["QB200_FUSED_LOG2T"] = old_t
-    for path in ("fused", "fused17", "general"):
-        for a, b in zip(res["token"], res[path]):
-            assert np.array_equal(a, b), path
+    for path in ("token", "general"):
+        os.environ["QB200_PATH"] = path
+        out, oco, st = qb.batch.stream_feed_batch(table, _t(data, dev), _t(chunk_off, dev), _t(stream_off, dev), None,
+                                                  flush=flush)
+        torch.cuda.synchronize()
+        n = int(oco[-1].item())
+        res[path] = (out[:n].cpu().numpy(), oco.cpu().numpy(), st.cpu().numpy())
+    for a, b in zip(res["token"], res["general"]):
+        assert np.array_equal(a, b)
     return res["token"]
 
 
@@ -102,24 +93,18 @@ def test_strip_paths_agree(qb, path_env):
     from oracle import c_oracle
     for streaming in (True, False):
         res = {}
-        try:
-            for path in ("token", "fused", "fused18", "general"):   # fused18: 256 KiB windows (tiles of many requests)
-                os.environ["QB200_PATH"] = path[:5]
-                if path == "fused18":
-                    os.environ["QB200_FUSED_LOG2T"] = "18"
-                out, off, rl = qb.batch.strip_concat_batch(table, _t(data, dev), _t(in_off, dev), _t(req_off, dev), sep, hide=True,
-                                                           streaming=streaming, want_resp_len=True)
-                torch.cuda.synchronize()
-                n = int(off[-1].item())
-                res[path] = (out[:n].cpu().numpy(), off.cpu().numpy(), rl.cpu().numpy()[: len(units)])
-        finally:
-            os.environ.pop("QB200_FUSED_LOG2T", None)
-        for path in ("fused", "fused18", "general"):
-            for a, b in zip(res["token"], res[path]):
-                assert np.array_equal(a, b), (path, streaming)
+        for path in ("token", "general"):
+            os.environ["QB200_PATH"] = path
+            out, off, rl = qb.batch.strip_concat_batch(table, _t(data, dev), _t(in_off, dev), _t(req_off, dev), sep, hide=True,
+                                                       streaming=streaming, want_resp_len=True)
+            torch.cuda.synchronize()
+            n = int(off[-1].item())
+            res[path] = (out[:n].cpu().numpy(), off.cpu().numpy(), rl.cpu().numpy()[: len(units)])
+        for a, b in zip(res["token"], res["general"]):
+            assert np.array_equal(a, b), streaming
         flags = c_oracle.FLAG_HIDE | (c_oracle.FLAG_STREAM_JOIN if streaming else 0)
         e_out, e_off, _ = c_oracle.strip_concat_batch(c_oracle.Tags(synth.TAGS5), data, in_off, req_off, synth.SEP_MULTIBYTE.encode(), flags)
-        assert np.array_equal(res["fused"][1], e_off) and np.array_equal(res["fused"][0], e_out)
+        assert np.array_equal(res["token"][1], e_off) and np.array_equal(res["token"][0], e_out)
 
 
 def test_record_slot_overflow_falls_back(qb):
@@ -191,7 +176,7 @@ def test_cfg2_full_size_sampled_against_oracle(qb):
     assert np.array_equal(depth, e_st["depth"][idx])
 
 
-@pytest.mark.parametrize("path", ["fused", "token", "general"])
+@pytest.mark.parametrize("path", ["token", "general"])
 def test_chained_slices_and_pipelined_host_feeder(qb, path_env, path):
     """QB200_CHAIN: a batch fed slice by slice (what the host-buffer session does to overlap PCIe copies with compute)
     gives the same bytes and the same per-chunk offsets as one call, whichever implementation takes the first slice."""
@@ -243,7 +228,7 @@ def test_chained_slices_and_pipelined_host_strip_concat(qb):
             assert np.array_equal(sess.h_out[: int(exp_off[-1])].numpy(), exp_out), (streaming, slices)
 
 
-@pytest.mark.parametrize("path", ["fused", "token"])
+@pytest.mark.parametrize("path", ["general"])
 def test_chained_slices_strip_concat_paths(qb, path_env, path):
     os.environ["QB200_PATH"] = path
     test_chained_slices_and_pipelined_host_strip_concat(qb)
@@ -286,14 +271,12 @@ def test_cfg3_cfg4_full_size_sampled_against_oracle(qb, cfg):
         assert bytes(out[got_off[q]:got_off[q + 1]].cpu().numpy()) == sep.join(parts)
 
 
-@pytest.mark.parametrize("path", ["fused", "token"])
-def test_small_grid_blocks_loop_and_take_many_tickets(qb, monkeypatch, path):
-    """QB200_GRID_CAP=3: every kernel runs with three blocks, so blocks loop over many groups and the look-back sees
-    blocks that each took dozens (fused: hundreds) of tickets.  Same bytes as the oracle."""
+def test_small_grid_blocks_loop_and_take_many_tickets(qb, monkeypatch):
+    """QB200_GRID_CAP=3: every warp-per-unit / lane-per-unit kernel runs with three blocks, so blocks loop over many groups
+    and the count kernel's look-back sees blocks that each took dozens of tickets.  Same bytes as the oracle."""
     from oracle import c_oracle
     from quorum_b200 import synth
     monkeypatch.setenv("QB200_GRID_CAP", "3")
-    monkeypatch.setenv("QB200_PATH", path)
     dev = torch.device("cuda", 0)
     base = synth.cfg2_base(64)
     n = 20000

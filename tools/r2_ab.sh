@@ -1,6 +1,6 @@
 #!/bin/bash
 # A/B of the implementations behind the ABI on one GPU: device-resident timing only (no CPU leg, no e2e).
-# usage: tools/r2_ab.sh "cfg2 cfg3" "fused token"  [extra env assignments]
+# usage: tools/r2_ab.sh "cfg2 cfg3" "token general"  [extra env assignments]
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 for wl in $1; do

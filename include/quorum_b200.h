@@ -81,6 +81,9 @@ void qb200_tags_destroy(qb200_tags *tags);
  * Outputs: request q's text is out_bytes[out_off[q] .. out_off[q+1]) (out_off has n_req+1 entries, out_off[0]=0);
  * resp_out_len (optional, n_resp entries) receives each response's filtered length (0 for excluded ones).
  * out_capacity must be >= in_off[n_resp] + sep_len * n_resp.   in_bytes and out_bytes must be 16-byte aligned.
+ * (out_capacity also sizes the scratch tables, see the *_scratch_bytes query.  A caller that knows its output is shorter and
+ * states a capacity below the input size still gets exact results as long as out_bytes holds the output: the units that
+ * lie beyond the stated bound are walked from their bytes, the slow way, instead of from the token records.)
  * QB200_CHAIN feeds one large batch slice by slice (to overlap host<->device copies with compute): in_bytes and
  * out_bytes stay those of the whole batch, `in_off` points at the slice's first response (entries still absolute byte
  * offsets), `req_off` holds the slice's requests as response indices relative to that first response, `out_off` points at
@@ -198,8 +201,9 @@ int64_t qb200_launch_count(void);
 /* Per-kernel split of the calls made between the two functions, without a profiler attached: while enabled, the library
  * records a CUDA event on the launching stream after each of its kernel launches.  qb200_profile_end synchronises on the
  * last event and returns the number of launches seen (at most max_entries are written): names[i] is a static string
- * (the kernel), ms[i] the time from the previous event to this one.  Measurement aid for bench.py; process-wide, not
- * thread-safe, no counterpart in the reference. */
+ * (the kernel), ms[i] the time from the previous event to this one.  Measurement aid for bench.py; process-wide;
+ * launches from several host threads are recorded safely (one list, mutex), begin / end themselves are for one thread at a
+ * time; no counterpart in the reference. */
 int qb200_profile_begin(void *stream);
 int32_t qb200_profile_end(const char **names, float *ms, int32_t max_entries);
 

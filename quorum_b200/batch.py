@@ -59,8 +59,8 @@ def tag_table(tags: Sequence[str]) -> TagTable:
     key = tuple(tags)
     t = _TABLES.get(key)
     if t is None:
-        if len(_TABLES) > 256:
-            _TABLES.clear()
+        if len(_TABLES) >= 256:                       # bounded: drop the oldest entry, not the whole cache
+            _TABLES.pop(next(iter(_TABLES)))
         t = _TABLES[key] = TagTable(key)
     return t
 
@@ -213,8 +213,8 @@ def pack_host(items: Sequence[bytes]) -> Tuple[torch.Tensor, torch.Tensor]:
     torch.cumsum(lens, 0, out=off[1:])
     total = int(off[-1])
     data = torch.frombuffer(bytearray(b"".join(items)), dtype=torch.uint8) if total else torch.empty(0, dtype=torch.uint8)
-    if torch.cuda.is_available():
-        data, off = data.pin_memory(), off.pin_memory()
+    if torch.cuda.is_available() and total >= (1 << 20):   # pinning costs a cudaHostAlloc: only worth it for real batches
+        data, off = data.pin_memory(), off.pin_memory()    # (the per-call drop-ins feed a few hundred bytes at a time)
     return data, off
 
 

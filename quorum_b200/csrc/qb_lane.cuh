@@ -128,7 +128,7 @@ __device__ __forceinline__ bool stream_walk_lane(const DevTags& tg, const uint8_
           unsigned long long cpack = 0;
 #pragma unroll
           for (int i = 0; i < 8; i++)
-              if (s0 + i <= s_last) cpack |= (unsigned long long)ts.cnt[s0 + i] << (8 * i);
+              if (s0 + i <= s_last) cpack |= (unsigned long long)ts.count(s0 + i) << (8 * i);
           if (cpack == 0) continue;
 #pragma unroll
           for (int i = 0; i < 8; i++)
@@ -268,7 +268,7 @@ __device__ __forceinline__ bool for_each_record(const TokSrc& ts, int64_t s_firs
         unsigned long long cpack = 0;
 #pragma unroll
         for (int i = 0; i < 8; i++)
-            if (s0 + i <= s_last) cpack |= (unsigned long long)ts.cnt[s0 + i] << (8 * i);
+            if (s0 + i <= s_last) cpack |= (unsigned long long)ts.count(s0 + i) << (8 * i);
         if (cpack == 0) continue;
 #pragma unroll
         for (int i = 0; i < 8; i++)

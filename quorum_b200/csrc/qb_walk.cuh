@@ -22,6 +22,10 @@ constexpr int kRecOverflow = 255;
 struct TokSrc {
     const uint8_t* cnt = nullptr;
     const uint32_t* rec = nullptr;
+    int64_t nsteps = 0;  // steps the record arrays were sized for (from the caller's byte bound, out_capacity)
+    // Record count of step s.  A step beyond the arrays reads as "overflowed": when a caller states a byte bound below the
+    // real input size the units out there are walked from their bytes instead of from records that were never written.
+    __device__ __forceinline__ int count(int64_t s) const { return s < nsteps ? (int)cnt[s] : kRecOverflow; }
 };
 __device__ __forceinline__ uint32_t rec_select(const uint4& a, const uint4& b, int k) {
     switch (k) {
@@ -61,7 +65,7 @@ __device__ inline bool unit_has_overflow(const TokSrc& ts, int64_t ustart, int64
     if (!ts.cnt || n <= 0) return false;
     const int64_t s0 = ustart >> 10, s1 = (ustart + n - 1) >> 10;
     bool bad = false;
-    for (int64_t s = s0 + lane; s <= s1; s += 32) bad |= ts.cnt[s] == kRecOverflow;
+    for (int64_t s = s0 + lane; s <= s1; s += 32) bad |= ts.count(s) == kRecOverflow;
     return __any_sync(kFull, bad);
 }
 
@@ -729,7 +733,7 @@ struct StreamRunWalker {
                     int cnt = 0;
                     uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
                     if (sj <= s_last) {
-                        cnt = ts.cnt[sj];
+                        cnt = ts.count(sj);
                         if (cnt == kRecOverflow) cnt = -1;
                         if (cnt > 0) {
                             const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);
@@ -914,7 +918,7 @@ struct StripRunWalker {
                 if (pass == 0 || !one_group) {
                     cnt = 0;
                     if (sj <= s_last) {
-                        cnt = ts.cnt[sj];
+                        cnt = ts.count(sj);
                         if (cnt == kRecOverflow) cnt = -1;
                         if (cnt > 0) {
                             const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);

@@ -14,6 +14,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <mutex>
 #include <vector>
 #include <new>
 
@@ -50,15 +51,17 @@ static int fail(int code, const char* fmt, const char* a = "") {
 // Every kernel launch goes through here: the launch counter, and (qb200_profile_begin) a CUDA event after the launch on
 // the launching stream so that a benchmark can read the per-kernel split of a call without a profiler attached.
 struct ProfMark { const char* name; cudaEvent_t ev; };
-static bool g_prof_on = false;
+static std::atomic<bool> g_prof_on{false};
+static std::mutex g_prof_mu;  // the mark list is shared by every thread that launches while profiling is on
 static std::vector<ProfMark> g_prof;
 static void prof_mark(const char* name, cudaStream_t stream) {
     ProfMark m{name, nullptr};
     if (cudaEventCreate(&m.ev) != cudaSuccess) return;
     cudaEventRecord(m.ev, stream);
+    std::lock_guard<std::mutex> lk(g_prof_mu);
     g_prof.push_back(m);
 }
-#define LAUNCHED(name) do { g_launches.fetch_add(1, std::memory_order_relaxed); if (g_prof_on) prof_mark(name, stream); } while (0)
+#define LAUNCHED(name) do { g_launches.fetch_add(1, std::memory_order_relaxed); if (g_prof_on.load(std::memory_order_relaxed)) prof_mark(name, stream); } while (0)
 
 // ---------------------------------------------------------------------------------------------------------------
 // Byte-rescanning walkers, out of line: used when no tokenizer records exist (QB200_PATH=general, the no-alloc entry
@@ -738,8 +741,11 @@ int64_t qb200_launch_count(void) { return g_launches.load(); }
 
 int qb200_profile_begin(void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
-    for (auto& m : g_prof) cudaEventDestroy(m.ev);
-    g_prof.clear();
+    {
+        std::lock_guard<std::mutex> lk(g_prof_mu);
+        for (auto& m : g_prof) cudaEventDestroy(m.ev);
+        g_prof.clear();
+    }
     g_prof_on = true;
     prof_mark("(begin)", stream);
     return QB200_OK;
@@ -747,6 +753,7 @@ int qb200_profile_begin(void* stream_) {
 
 int32_t qb200_profile_end(const char** names, float* ms, int32_t max_entries) {
     g_prof_on = false;
+    std::lock_guard<std::mutex> lk(g_prof_mu);
     int32_t n = 0;
     if (!g_prof.empty()) CUDA_TRY(cudaEventSynchronize(g_prof.back().ev));
     for (size_t i = 1; i < g_prof.size(); i++) {
@@ -878,6 +885,7 @@ static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const in
     LAUNCHED("tokenize_kernel");
     ts.cnt = cnt;
     ts.rec = rec;
+    ts.nsteps = st;
     return ts;
 }
 

@@ -298,3 +298,38 @@ def test_small_grid_blocks_loop_and_take_many_tickets(qb, monkeypatch):
                                               streaming=False)
     torch.cuda.synchronize()
     assert np.array_equal(off2.cpu().numpy(), e_off) and np.array_equal(o2[: int(e_off[-1])].cpu().numpy(), e_out)
+
+
+def test_capacity_below_the_input_size_stays_exact(qb):
+    """A caller whose output is known to be short may pass out_bytes (and so out_capacity, which sizes the token-record
+    tables) smaller than the input: the units beyond the stated bound must be walked from their bytes, not from record
+    slots that were never written."""
+    from oracle import c_oracle
+    from quorum_b200 import synth
+    dev = torch.device("cuda", 0)
+    base = synth.cfg4_base(24, 32768)                                  # 70 % of every response is removed
+    data = np.ascontiguousarray(base).reshape(-1)
+    in_off = np.arange(0, data.size + 1, 32768, dtype=np.int64)
+    req_off = np.arange(0, base.shape[0] + 1, 8, dtype=np.int64)
+    sep = b"\n--\n"
+    e_out, e_off, _ = c_oracle.strip_concat_batch(c_oracle.Tags(synth.TAGS5), data, in_off, req_off, sep, c_oracle.FLAG_HIDE)
+    cap = int(e_off[-1]) + 4096
+    assert cap < data.size // 2
+    out = torch.zeros(cap, dtype=torch.uint8, device=dev)
+    got, off, _ = qb.batch.strip_concat_batch(qb.batch.tag_table(synth.TAGS5), _t(data, dev), _t(in_off, dev), _t(req_off, dev),
+                                              _t(np.frombuffer(sep, dtype=np.uint8), dev), hide=True, streaming=False, out_bytes=out)
+    torch.cuda.synchronize()
+    assert np.array_equal(off.cpu().numpy(), e_off) and np.array_equal(got[: int(e_off[-1])].cpu().numpy(), e_out)
+    # streams: half of every stream is inside thinking blocks
+    sb = synth.cfg2_base(40)
+    sdata = np.ascontiguousarray(sb).reshape(-1)
+    chunk_off = np.arange(0, sdata.size + 1, 64, dtype=np.int64)
+    stream_off = np.arange(0, 40 * 256 + 1, 256, dtype=np.int64)
+    s_out, s_oco, _ = c_oracle.stream_feed_batch(c_oracle.Tags(synth.TAGS5), sdata, chunk_off, stream_off, None, c_oracle.FLAG_FLUSH)
+    cap = int(s_oco[-1]) + 4096
+    assert cap < sdata.size
+    out = torch.zeros(cap, dtype=torch.uint8, device=dev)
+    got, oco, _ = qb.batch.stream_feed_batch(qb.batch.tag_table(synth.TAGS5), _t(sdata, dev), _t(chunk_off, dev), _t(stream_off, dev),
+                                             None, flush=True, out_bytes=out)
+    torch.cuda.synchronize()
+    assert np.array_equal(oco.cpu().numpy(), s_oco) and np.array_equal(got[: int(s_oco[-1])].cpu().numpy(), s_out)

@@ -422,7 +422,7 @@ def make_workload(ctx, name, wl, units_override=0, shard=None):
             b0, b1 = int(off_all[lo * pr]), int(off_all[hi * pr])
             start = b0 % pool.size
             k = (start + (b1 - b0) + pool.size - 1) // pool.size
-            data = torch.from_numpy(pool.copy()).to(dev).repeat(max(k, 1))[start:start + (b1 - b0)].contiguous()
+            data = torch.from_numpy(pool.copy()).to(dev).repeat(max(k, 1))[start:start + (b1 - b0)].clone()   # fresh, 16-byte aligned
             lens = torch.from_numpy(lens_all[lo * pr:hi * pr].copy()).to(dev)
             W.shard_info = {"requests": [int(lo), int(hi)], "of_requests": int(len(req_bytes)), "bytes": b1 - b0,
                             "total_bytes": int(off_all[-1]), "parts_bytes": [int(off_all[h * pr] - off_all[l * pr]) for l, h in parts]}

@@ -4,8 +4,8 @@
 //   stream_feed :  tokenize (one record per '<')  ->  count (lane per stream: automaton over the records, descriptor,
 //                  carried state, prefix sum over the streams by look-back)  ->  offsets (thread per feed boundary)
 //                  ->  finish (warp per stream: kept runs to their final place)
-//   strip_concat:  tokenize  ->  count (lane per response: liveness, automaton, strip(), descriptor)  ->  request layout,
-//                  scan, finalize (per-request prefix sums incl. separators)  ->  copy (warp per response)
+//   strip_concat:  tokenize  ->  count (lane per response: liveness, automaton, strip(), descriptor / run pool)  ->  request
+//                  offsets (per-request lengths incl. separators, prefix sum by look-back)  ->  copy (warp per response)
 // QB200_PATH=general: the byte-rescanning warp-per-unit walkers (count, scan, copy).
 // Then the rows around the filter: SSE framing (qb_sse.cuh), SSE parsing (qb_ssein.cuh), aggregate prompts (qb_agg.cuh).
 #include <cuda_runtime.h>
@@ -200,29 +200,6 @@ strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
     }
 }
 
-// one thread per request: relative offsets of its responses (separators included) and the request's total length
-__global__ void request_layout_kernel(const int64_t* __restrict__ in_off, const int64_t* __restrict__ req_off,
-                                      int64_t n_req, const int64_t* __restrict__ klen, int hide, int stream_join,
-                                      int32_t sep_len, int64_t* __restrict__ dst, int64_t* __restrict__ reqlen) {
-    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= n_req) return;
-    const int64_t r0 = req_off ? req_off[q] : q, r1 = req_off ? req_off[q + 1] : q + 1;
-    int64_t o = 0;
-    bool first = true;
-    for (int64_t r = r0; r < r1; r++) {
-        const int64_t len = in_off[r + 1] - in_off[r];
-        if (stream_join && len == 0) {  // oai_proxy.py:763 `if text`
-            dst[r] = -1;
-            continue;
-        }
-        if (!first) o += sep_len;
-        dst[r] = (o << 1) | (first ? 0 : 1);  // bit 0: a separator sits right before this response's text
-        first = false;
-        o += hide ? klen[r] : len;
-    }
-    reqlen[q] = o;
-}
-
 // Exclusive scan of v[0..n) into out[0..n], out[n] = total, in three small launches:
 //   scan_partials_kernel   block b sums its slice of kScanSlice elements            -> partial[b]
 //   scan_kernel            one block scans the (few) partials in place               -> partial[b] = offset of slice b
@@ -342,15 +319,81 @@ static void launch_scan(const int64_t* v, int64_t n, int64_t* out, int64_t* part
     LAUNCHED("scan_apply_kernel");
 }
 
-// dst[r] += out_off[request of r]   (thread per request)
-__global__ void request_finalize_kernel(const int64_t* __restrict__ req_off, int64_t n_req,
-                                        const int64_t* __restrict__ out_off, int64_t* __restrict__ dst) {
-    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= n_req) return;
-    const int64_t r0 = req_off ? req_off[q] : q, r1 = req_off ? req_off[q + 1] : q + 1;
-    const int64_t base = out_off[q];
-    for (int64_t r = r0; r < r1; r++)
-        if (dst[r] >= 0) dst[r] += base << 1;
+// The join layout in one kernel (instead of layout, a three-kernel scan and finalize): a block takes 256 consecutive
+// requests by ticket, a thread sums its request (kept lengths + separators), block scan + decoupled look-back over the
+// blocks give the request's output offset, then the thread writes its responses' destinations.
+struct ReqScan {
+    unsigned long long* state;  // one look-back word per block of 256 requests (zeroed before the launch)
+    unsigned int* ticket;
+    int chain;                  // out_off[0] already holds where this call's output starts
+};
+__global__ void __launch_bounds__(256)
+request_offsets_kernel(const int64_t* __restrict__ in_off, const int64_t* __restrict__ req_off, int64_t n_req,
+                       const int64_t* __restrict__ klen, int hide, int stream_join, int32_t sep_len, int64_t* __restrict__ dst,
+                       int64_t* __restrict__ out_off, ReqScan scan) {
+    __shared__ int64_t s_wsum[8];
+    __shared__ int64_t s_excl, s_ticket;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t init = scan.chain ? out_off[0] : 0;
+    const int64_t nblk = (n_req + 255) >> 8;
+    for (;;) {
+        if (threadIdx.x == 0) s_ticket = (int64_t)atomicAdd(scan.ticket, 1u);
+        __syncthreads();
+        const int64_t t = s_ticket;
+        if (t >= nblk) break;
+        const int64_t q = (t << 8) + threadIdx.x;
+        int64_t r0 = 0, r1 = 0, len = 0;
+        if (q < n_req) {
+            r0 = req_off ? req_off[q] : q;
+            r1 = req_off ? req_off[q + 1] : q + 1;
+            bool first = true;
+            for (int64_t r = r0; r < r1; r++) {
+                const int64_t l = in_off[r + 1] - in_off[r];
+                if (stream_join && l == 0) continue;  // oai_proxy.py:763 `if text`
+                if (!first) len += sep_len;
+                first = false;
+                len += hide ? klen[r] : l;
+            }
+        }
+        int64_t incl = len;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int64_t v = __shfl_up_sync(kFull, incl, d);
+            if (lane >= d) incl += v;
+        }
+        if (lane == 31) s_wsum[wib] = incl;
+        __syncthreads();
+        int64_t before = 0, block_tot = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++) {
+            const int64_t v = s_wsum[w];
+            if (w < wib) before += v;
+            block_tot += v;
+        }
+        if (wib == 0) {
+            const int64_t excl = lookback_exclusive(scan.state, t, block_tot, lane);
+            if (lane == 0) s_excl = excl;
+        }
+        __syncthreads();
+        if (q < n_req) {
+            const int64_t base = init + s_excl + before + incl - len;
+            out_off[q] = base;
+            if (q == n_req - 1) out_off[n_req] = base + len;
+            int64_t o = 0;
+            bool first = true;
+            for (int64_t r = r0; r < r1; r++) {
+                const int64_t l = in_off[r + 1] - in_off[r];
+                if (stream_join && l == 0) {
+                    dst[r] = -1;
+                    continue;
+                }
+                if (!first) o += sep_len;
+                dst[r] = ((base + o) << 1) | (first ? 0 : 1);  // bit 0: a separator sits right before this response's text
+                first = false;
+                o += hide ? klen[r] : l;
+            }
+        }
+    }
 }
 
 // Warp-cooperative copy of a unit's kept runs (descriptor) to dst: run i goes to dst + held_kept + (lengths before it).
@@ -972,27 +1015,34 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     uint8_t* tok_scratch = (uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp);
     const int lane_steps = env_int("QB200_LANE_STEPS", 72);  // 0: warp per response only
     const int path = path_choice();
+    // words that must start at zero: the look-back words + ticket of request_offsets_kernel, then the run pool's counter
+    // (they live in the `reqlen` part of the scratch; the tokenizer kernel clears them, else a memset)
+    unsigned long long* scan_words = (unsigned long long*)reqlen;
+    const int64_t nblk_req = (n_req + 255) >> 8;
     RunPool pool;
+    pool.top = scan_words + nblk_req + 2;
     if (hide && n_resp > 0 && path != kPathGeneral) {
         uint8_t* pp = tok_scratch + tok_scratch_bytes(out_capacity);
-        pool.top = (unsigned long long*)pp;
         pool.runs = (int2*)(pp + 256);
         pool.cap = pool_slots(out_capacity);
-        ts = launch_tokenizer(tags->dev, in_bytes, in_off, nullptr, n_resp, out_capacity, tok_scratch, stream, pool.top, 1);
+        ts = launch_tokenizer(tags->dev, in_bytes, in_off, nullptr, n_resp, out_capacity, tok_scratch, stream, scan_words, nblk_req + 3);
+    } else {
+        CUDA_TRY(cudaMemsetAsync(scan_words, 0, (size_t)(nblk_req + 3) * 8, stream));
     }
     if (hide && n_resp > 0) {
         strip_count_kernel<<<grid_for((n_resp + 31) / 32), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts,
                                                                                  ts.cnt ? desc : nullptr, lane_steps, pool);
         LAUNCHED("strip_count_kernel");
     }
-    const int tb = 256;
-    const unsigned rg = (unsigned)((n_req + tb - 1) / tb);
-    request_layout_kernel<<<rg, tb, 0, stream>>>(in_off, req_off, n_req, klen, hide, sj, sep_len, dst, reqlen);
-    LAUNCHED("request_layout_kernel");
-    launch_scan(reqlen, n_req, out_off, (int64_t*)((uint8_t*)reqlen + align256((size_t)(n_req + 2) * 8)), stream,
-                chain ? out_off : nullptr, nullptr);
-    request_finalize_kernel<<<rg, tb, 0, stream>>>(req_off, n_req, out_off, dst);
-    LAUNCHED("request_finalize_kernel");
+    {
+        ReqScan rs;
+        rs.state = scan_words;
+        rs.ticket = (unsigned int*)(scan_words + nblk_req + 1);
+        rs.chain = chain ? 1 : 0;
+        int64_t g = nblk_req < 148 * 8 ? nblk_req : 148 * 8;
+        request_offsets_kernel<<<(unsigned)(g < 1 ? 1 : g), 256, 0, stream>>>(in_off, req_off, n_req, klen, hide, sj, sep_len, dst, out_off, rs);
+        LAUNCHED("request_offsets_kernel");
+    }
     if (n_resp > 0) {
         strip_copy_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, dst,
                                                                     hide, sep, sep_len, out_bytes, resp_out_len,

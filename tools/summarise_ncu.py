@@ -6,9 +6,14 @@ import os
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-rnd = sys.argv[1] if len(sys.argv) > 1 else "r1"
+rnd = sys.argv[1] if len(sys.argv) > 1 else "r2"
+import subprocess
+try:
+    commit = subprocess.check_output(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], text=True).strip()
+except Exception:
+    commit = None
 traffic, md = {}, ["| workload | kernel | launches/call | avg us (ncu, cold) | share | DRAM read MB | DRAM write MB |", "|---|---|---|---|---|---|---|"]
-for wl in ("cfg2", "cfg3", "cfg4"):
+for wl in ("cfg2", "cfg3", "cfg4", "cfg5"):
     path = os.path.join(ROOT, "profiles", f"{rnd}_ncu_launches_{wl}.csv")
     if not os.path.isfile(path):
         continue
@@ -19,7 +24,7 @@ for wl in ("cfg2", "cfg3", "cfg4"):
     ids = set()
     for r in rows[1:]:
         name = r[ki].split("(")[0].replace("qb::", "").replace("void ", "")
-        if not any(t in name for t in ("tokenize", "stream_", "strip_", "scan", "request_", "sse_", "assemble")):
+        if not any(t in name for t in ("tokenize", "stream_", "strip_", "scan", "request_", "sse_", "assemble", "set_i64")):
             continue
         v = float(r[vi].replace(",", ""))
         if r[mi] == "gpu__time_duration.sum":
@@ -30,7 +35,7 @@ for wl in ("cfg2", "cfg3", "cfg4"):
     # bench.py --steps 2 --warmup 3 = 5 timed-style calls + 2 profile-pass calls: launches per call = count / calls
     calls = max(len(per.get("tokenize_kernel", {}).get("gpu__time_duration.sum", [])), 1)
     tot_us = sum(sum(m["gpu__time_duration.sum"]) for m in per.values()) / calls
-    entry = {"per_kernel": {}, "source": f"ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none; profiles/{rnd}_ncu_launches_{wl}.csv"}
+    entry = {"per_kernel": {}, "commit": commit, "source": f"ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none; profiles/{rnd}_ncu_launches_{wl}.csv"}
     dram_total = 0.0
     for name, m in per.items():
         n = len(m["gpu__time_duration.sum"])

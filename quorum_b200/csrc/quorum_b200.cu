@@ -23,6 +23,7 @@
 #include "qb_scan.cuh"
 #include "qb_tok.cuh"
 #include "qb_lane.cuh"
+#include "qb_scanwalk.cuh"
 #include "qb_sse.cuh"
 #include "qb_agg.cuh"
 #include "qb_ssein.cuh"
@@ -117,6 +118,18 @@ __device__ __noinline__ StripResult strip_count_warp(const DevTags& tg, const ui
     }
     return res;
 }
+// one response by the whole warp, out of line: long responses go to the scan walker (lanes own steps, state carried by the
+// scan of transition vectors, qb_scanwalk.cuh); what it cannot take goes to the run-list warp walker, then to the byte walker
+__device__ __noinline__ StripResult strip_count_unit(const DevTags& tg, const uint8_t* in, int64_t total, int64_t a, int64_t n,
+                                                     unsigned long long* lc, int2* stage, int lane, TokSrc ts, UnitDesc* desc,
+                                                     const RunPool& pool, int scanwalk) {
+    StripResult res;
+    res.first_pos = 0;
+    res.kept_len = 0;
+    if (!ts.cnt) return strip_count_slow(tg, in, total, a, n, lc, lane);
+    if (scanwalk && strip_scan_walk(tg, in, a, n, ts, desc, &res.kept_len, lc, stage, pool, lane)) return res;
+    return strip_count_warp(tg, in, total, a, n, lc, lane, ts, desc);
+}
 __device__ __noinline__ StreamResult stream_count_slow(const DevTags& tg, const uint8_t* bytes, int64_t total, const int64_t* co,
                                                        int64_t m, int lane, uint32_t flags, const StreamState* st_in) {
     StreamWalker<false> w(tg, bytes, total, co, m, lane, flags);
@@ -157,17 +170,24 @@ __device__ __forceinline__ void prefetch_unit_meta(const TokSrc& ts, const uint8
 
 // scratch layout for strip_concat: int64 klen[n_resp] | int64 first[n_resp] | int64 dst[n_resp] | int64 reqlen[n_req+1]
 // (five or six blocks per SM - 48 / 40 registers - change nothing: cfg3 0.221 / 0.226 ms against 0.217)
+//
+// A warp takes 32 consecutive responses, one per lane (qb_lane.cuh).  The ones a lane cannot take (longer than lane_steps,
+// more classes than a lane tracks, pool exhausted, an overflowed step) need a whole warp each; they go to a queue that
+// strip_count_long_kernel drains with every warp of the GPU, one response per warp - walked where they are found, 32 long
+// responses would run one after the other on ONE warp (a batch of 4,096 responses of 256 KiB ran on 128 warps: 1.5 ms).
+struct LongQueue {
+    int64_t* items = nullptr;          // response indices (the `dst` array, not needed before the request offsets)
+    unsigned long long* count = nullptr;
+};
 __global__ void __launch_bounds__(kThreads, 4)
 strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
                    int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first, TokSrc ts,
-                   UnitDesc* __restrict__ desc, int lane_steps, RunPool pool) {
+                   UnitDesc* __restrict__ desc, int lane_steps, RunPool pool, LongQueue lq) {
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     __shared__ int s_lc[kLaneCls][kThreads];  // lane walker: last closer per class, one column per thread
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
     const int64_t ngroups = (n_resp + 31) >> 5;
-    // a warp takes 32 consecutive responses, one per lane (qb_lane.cuh); the ones too long for a lane or that do not fit
-    // a descriptor are then walked one at a time by the whole warp
     for (int64_t g = (int64_t)blockIdx.x * kWarpsPerBlock + wib; g < ngroups; g += (int64_t)gridDim.x * kWarpsPerBlock) {
         const int64_t r = (g << 5) + lane;
         const bool have = r < n_resp;
@@ -180,14 +200,25 @@ strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
         }
         __syncwarp();
         unsigned todo = __ballot_sync(kFull, have && !done);
-        while (todo) {  // one warp per response
+        if (ts.cnt) {  // record-driven call: the leftovers wait for strip_count_long_kernel
+            if (todo) {
+                unsigned long long at = 0;
+                const int leader = __ffs(todo) - 1;
+                if (lane == leader) at = atomicAdd(lq.count, (unsigned long long)__popc(todo));
+                at = __shfl_sync(kFull, at, leader);
+                if (have && !done) lq.items[at + __popc(todo & ((1u << lane) - 1u))] = r;
+            }
+            if (have && done) {
+                klen[r] = kl;
+                first[r] = fp;
+            }
+            continue;
+        }
+        while (todo) {  // no records (QB200_PATH=general): one warp per response, from the bytes
             const int j = __ffs(todo) - 1;
             todo &= todo - 1;
-            const int64_t rj = (g << 5) + j;
             const int64_t aj = __shfl_sync(kFull, a, j), bj = __shfl_sync(kFull, b, j);
-            StripResult res;
-            if (ts.cnt) res = strip_count_warp(tg, in, total, aj, bj - aj, lastclose[wib], lane, ts, desc + rj);
-            else res = strip_count_slow(tg, in, total, aj, bj - aj, lastclose[wib], lane);
+            const StripResult res = strip_count_slow(tg, in, total, aj, bj - aj, lastclose[wib], lane);
             if (lane == j) {
                 kl = res.kept_len;
                 fp = res.first_pos;
@@ -198,6 +229,28 @@ strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict
             klen[r] = kl;
             first[r] = fp;
         }
+    }
+}
+
+// the queued responses, one per warp, over the whole GPU
+__global__ void __launch_bounds__(kThreads, 4)
+strip_count_long_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
+                        int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first, TokSrc ts,
+                        UnitDesc* __restrict__ desc, RunPool pool, LongQueue lq, int scanwalk) {
+    __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
+    __shared__ int2 s_stage[kWarpsPerBlock][kDescRuns + 1];  // scan walker: the runs of a unit that fits a descriptor
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t total = in_off[n_resp];
+    const int64_t nq = (int64_t)*lq.count;
+    for (int64_t i = (int64_t)blockIdx.x * kWarpsPerBlock + wib; i < nq; i += (int64_t)gridDim.x * kWarpsPerBlock) {
+        const int64_t r = lq.items[i];
+        const int64_t a = in_off[r], b = in_off[r + 1];
+        const StripResult res = strip_count_unit(tg, in, total, a, b - a, lastclose[wib], s_stage[wib], lane, ts, desc + r, pool, scanwalk);
+        if (lane == 0) {
+            klen[r] = res.kept_len;
+            first[r] = res.first_pos;
+        }
+        __syncwarp();
     }
 }
 
@@ -1023,18 +1076,26 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     const int64_t nblk_req = (n_req + 255) >> 8;
     RunPool pool;
     pool.top = scan_words + nblk_req + 2;
+    LongQueue lq;
+    lq.items = dst;
+    lq.count = scan_words + nblk_req + 3;
     if (hide && n_resp > 0 && path != kPathGeneral) {
         uint8_t* pp = tok_scratch + tok_scratch_bytes(out_capacity);
         pool.runs = (int2*)(pp + 256);
         pool.cap = pool_slots(out_capacity);
-        ts = launch_tokenizer(tags->dev, in_bytes, in_off, nullptr, n_resp, out_capacity, tok_scratch, stream, scan_words, nblk_req + 3);
+        ts = launch_tokenizer(tags->dev, in_bytes, in_off, nullptr, n_resp, out_capacity, tok_scratch, stream, scan_words, nblk_req + 4);
     } else {
-        CUDA_TRY(cudaMemsetAsync(scan_words, 0, (size_t)(nblk_req + 3) * 8, stream));
+        CUDA_TRY(cudaMemsetAsync(scan_words, 0, (size_t)(nblk_req + 4) * 8, stream));
     }
     if (hide && n_resp > 0) {
         strip_count_kernel<<<grid_for((n_resp + 31) / 32), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts,
-                                                                                 ts.cnt ? desc : nullptr, lane_steps, pool);
+                                                                                 ts.cnt ? desc : nullptr, lane_steps, pool, lq);
         LAUNCHED("strip_count_kernel");
+        if (ts.cnt) {
+            strip_count_long_kernel<<<4 * sm_count(), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts, desc, pool,
+                                                                            lq, env_int("QB200_SCANWALK", 1));
+            LAUNCHED("strip_count_long_kernel");
+        }
     }
     {
         ReqScan rs;

@@ -333,3 +333,33 @@ def test_capacity_below_the_input_size_stays_exact(qb):
                                              None, flush=True, out_bytes=out)
     torch.cuda.synchronize()
     assert np.array_equal(oco.cpu().numpy(), s_oco) and np.array_equal(got[: int(s_oco[-1])].cpu().numpy(), s_out)
+
+
+@pytest.mark.parametrize("scanwalk", ["1", "0"])
+def test_warp_walkers_for_long_responses_match_the_oracle(qb, monkeypatch, scanwalk):
+    """QB200_LANE_STEPS=1 sends every response that spans more than one KiB step to the warp walkers: the scan walker
+    (transition vectors composed by a warp scan, qb_scanwalk.cuh; QB200_SCANWALK=1, the default) or the run-list walker
+    behind it (QB200_SCANWALK=0).  Adversarial cfg5 mix plus long responses with hundreds of blocks, both join forms."""
+    from oracle import c_oracle
+    from quorum_b200 import synth
+    monkeypatch.setenv("QB200_LANE_STEPS", "1")
+    monkeypatch.setenv("QB200_SCANWALK", scanwalk)
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(17)
+    units = synth.cfg5_units(5 << 20, seed=97)
+    units += [bytes(synth.make_unit(rng, 200_000, 90, 0.5)), bytes(synth.make_unit(rng, 70_000, 3, 0.7)),
+              ("keep <think>drop</think> " * 3000).encode(), b"<think>" * 5000 + b"</think>", b" \n" * 40_000, b"x" * 100_000]
+    data, in_off = synth.pack(units)
+    req_off = np.unique(np.concatenate([[0, len(units)], rng.integers(0, len(units), len(units) // 4)])).astype(np.int64)
+    sep = synth.SEP_MULTIBYTE.encode()
+    table = qb.batch.tag_table(synth.TAGS5)
+    for streaming in (False, True):
+        flags = c_oracle.FLAG_HIDE | (c_oracle.FLAG_STREAM_JOIN if streaming else 0)
+        e_out, e_off, e_len = c_oracle.strip_concat_batch(c_oracle.Tags(synth.TAGS5), data, in_off, req_off, sep, flags)
+        out, off, rl = qb.batch.strip_concat_batch(table, _t(data, dev), _t(in_off, dev), _t(req_off, dev),
+                                                   _t(np.frombuffer(sep, dtype=np.uint8), dev), hide=True, streaming=streaming,
+                                                   want_resp_len=True)
+        torch.cuda.synchronize()
+        assert np.array_equal(rl.cpu().numpy()[: len(units)], e_len), streaming
+        assert np.array_equal(off.cpu().numpy(), e_off), streaming
+        assert np.array_equal(out[: int(e_off[-1])].cpu().numpy(), e_out), streaming

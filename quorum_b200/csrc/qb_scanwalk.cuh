@@ -7,8 +7,9 @@
 //   B  every lane folds the records of its step into a transition vector v[s] = state after the step when it is entered
 //      in state s (states: OUT, IN(c) for each class c; a live open tag sends OUT to IN(c), a close tag of class c sends
 //      IN(c) to OUT, everything else is the identity), five packed words, byte-parallel updates
-//   C  inclusive Hillis-Steele scan of the vectors over the lanes (composition (v2 . v1)[s] = v2[v1[s]]); the exclusive
-//      prefix applied to the state carried in from the previous 32 steps is the lane's entry state
+//   C  scan of the vectors over the lanes: applied in lane order to the state carried in from the previous 32 steps, which
+//      gives every lane its entry state (the composition of whole vectors, (v2 . v1)[s] = v2[v1[s]], in log2(32) rounds was
+//      built and measured slower, see below)
 //   D  every lane walks its records again from its entry state and emits the run ends (live open met in OUT) and run
 //      starts (matching close met in IN(c)); warp prefix sums rank them, the k-th start pairs with the k-th end
 //   E  empty runs dropped (compaction), `.strip()` at the two ends of the list, kept length; up to kDescRuns runs go to
@@ -45,24 +46,11 @@ __device__ __forceinline__ uint32_t bytes_replace(uint32_t w, uint32_t val, uint
     const uint32_t m = (t >> 7) * 0xFFu;   // 0xFF in those bytes
     return (w & ~m) | ((to * 0x01010101u) & m);
 }
-__device__ __forceinline__ void tvec_apply(TVec& v, int from, int to) {  // then: state `from` -> `to`
+__device__ __forceinline__ void tvec_apply(TVec& v, int from, int to, int nwords) {  // then: state `from` -> `to`
 #pragma unroll
-    for (int i = 0; i < 5; i++) v.w[i] = bytes_replace(v.w[i], (uint32_t)from, (uint32_t)to);
+    for (int i = 0; i < 5; i++)
+        if (i < nwords) v.w[i] = bytes_replace(v.w[i], (uint32_t)from, (uint32_t)to);
 }
-// first `a`, then `b`
-__device__ __forceinline__ TVec tvec_compose(const TVec& a, const TVec& b, int nstates) {
-    TVec r = tvec_identity();
-#pragma unroll
-    for (int s = 0; s < kLaneCls + 1; s++) {
-        if (s < nstates) {
-            const int mid = (int)((a.w[s >> 2] >> ((s & 3) * 8)) & 0xFFu);
-            const uint32_t out = (uint32_t)tvec_get(b, mid);
-            r.w[s >> 2] = (r.w[s >> 2] & ~(0xFFu << ((s & 3) * 8))) | (out << ((s & 3) * 8));
-        }
-    }
-    return r;
-}
-
 // first / last non-white byte of [s, e) of the unit (warp-cooperative), -1 when all white
 __device__ __forceinline__ int scan_first_nonwhite(const PtrAcc& T, int s, int e, int n, int lane) {
     for (int base = s; base < e; base += 32) {
@@ -87,7 +75,7 @@ __device__ __noinline__ bool strip_scan_walk(const DevTags& tg, const uint8_t* b
                                              const RunPool& pool, int lane) {
     if (n64 <= 0 || n64 >= (int64_t)1 << 31 || tg.ncls > kLaneCls) return false;
     const int n = (int)n64;
-    const int nstates = tg.ncls + 1;
+    const int nwords = (tg.ncls + 1 + 3) >> 2;
     const PtrAcc T{buf + ustart};
     const int64_t s_first = ustart >> 10, s_last = (ustart + n - 1) >> 10;
     for (int c = lane; c < tg.ncls; c += 32) lc[c] = 0;
@@ -157,25 +145,21 @@ __device__ __noinline__ bool strip_scan_walk(const DevTags& tg, const uint8_t* b
             if (kind == 2 || x < 0 || x + (int)((r >> 10) & 127) > n) continue;
             const int cls = (r >> 19) & 127;
             if (kind == 0) {
-                if (lc[cls] > (unsigned long long)x) tvec_apply(v, 0, cls + 1);  // live open tag: OUT -> IN(cls)
+                if (lc[cls] > (unsigned long long)x) tvec_apply(v, 0, cls + 1, nwords);  // live open tag: OUT -> IN(cls)
             } else {
-                tvec_apply(v, cls + 1, 0);                                        // close tag: IN(cls) -> OUT
+                tvec_apply(v, cls + 1, 0, nwords);                                       // close tag: IN(cls) -> OUT
             }
         }
-        // C: inclusive scan of the vectors over the lanes
-        TVec inc = v;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            TVec up;
-#pragma unroll
-            for (int i = 0; i < 5; i++) up.w[i] = __shfl_up_sync(kFull, inc.w[i], d);
-            if (lane >= d) inc = tvec_compose(up, inc, nstates);
+        // C: scan of the vectors over the lanes: applied in lane order to the state carried into the group, every lane
+        // keeps the state it is entered in.  32 dependent shuffle + lookup steps; the logarithmic form - five rounds of
+        // (v2 . v1)[s] = v2[v1[s]] over whole vectors - was measured slower (count of 4,096 x 256 KiB dense responses 0.174 vs
+        // 0.116 ms, cfg5 1.82 vs 1.74 ms): composing two vectors costs ~190 instructions, the lookup ten.
+        int state = carry, run_state = carry;
+        for (int l = 0; l < 32; l++) {
+            if (lane == l) state = run_state;
+            run_state = __shfl_sync(kFull, tvec_get(v, run_state), l);
         }
-        TVec exc;
-#pragma unroll
-        for (int i = 0; i < 5; i++) exc.w[i] = __shfl_up_sync(kFull, inc.w[i], 1);
-        int state = lane == 0 ? carry : tvec_get(exc, carry);
-        const int carry_next = __shfl_sync(kFull, tvec_get(inc, carry), 31);
+        const int carry_next = run_state;
         // D: events of this step from its entry state.  Two passes over the records: count, then (with the ranks) write.
         int nS = 0, nE = 0;
         {

@@ -135,6 +135,28 @@ __device__ __noinline__ StreamResult stream_count_slow(const DevTags& tg, const 
     StreamWalker<false> w(tg, bytes, total, co, m, lane, flags);
     return w.run(st_in, nullptr);
 }
+// one stream by the whole warp, out of line (the lane walker is the common case; inline, the warp walkers cost the count
+// kernel its registers): record-driven run-list walker, then the byte-rescanning walker
+__device__ __noinline__ StreamResult stream_count_unit(const DevTags& tg, const uint8_t* bytes, int64_t total, const int64_t* co, int64_t m,
+                                                       int lane, uint32_t flags, TokSrc ts, const StreamState* st_in, StreamState* st_out,
+                                                       StreamDesc* desc) {
+    StreamResult r;
+    bool slow = ts.cnt == nullptr;
+    if (!slow) {
+        StreamRunWalker w(tg, bytes, total, co, m, lane, flags, ts);
+        w.desc = desc;
+        if (m <= 0 && lane == 0) desc->nruns = desc->held_kept = 0;  // nothing fed: nothing to copy
+        // record-driven units get their carried state here (st_in may alias st_out; a unit that overflows returns before
+        // it writes any and is redone, state included, by the finish kernel)
+        r = w.run(st_in, st_out);
+        slow = w.overflow;  // does not fit the descriptor: redo this unit from its bytes
+    }
+    if (slow) {
+        r = stream_count_slow(tg, bytes, total, co, m, lane, flags, st_in);
+        if (desc && lane == 0) desc->nruns = -1;
+    }
+    return r;
+}
 __device__ __noinline__ void stream_copy_slow(const DevTags& tg, const uint8_t* bytes, int64_t total, const int64_t* co, int64_t m,
                                               int lane, uint32_t flags, const StreamState* st_in, StreamState* st_out,
                                               int64_t base, uint8_t* out, int64_t* out_chunk_off, int64_t c0) {
@@ -584,6 +606,7 @@ struct CountScan {
     const int64_t* init_arr;        // chained call: the first base is init_arr[*init_idx] (0 when null)
     const int64_t* init_idx;
 };
+// (two or three blocks per SM - 128 / 80 registers, no spills - change nothing: cfg2 46.2 / 47.7 us against 48.3)
 template <bool SCAN>
 __global__ void __launch_bounds__(kThreads, 4)
 stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ bytes,
@@ -633,21 +656,8 @@ stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restric
             todo &= todo - 1;
             const int64_t sj = (g << 5) + j;
             const int64_t d0 = __shfl_sync(kFull, c0, j), d1 = __shfl_sync(kFull, c1, j);
-            StreamResult r;
-            bool slow = ts.cnt == nullptr;
-            if (!slow) {
-                StreamRunWalker w(tg, bytes, total, chunk_off + d0, d1 - d0, lane, flags, ts);
-                w.desc = desc + sj;
-                if (d1 <= d0 && lane == 0) desc[sj].nruns = desc[sj].held_kept = 0;  // nothing fed: nothing to copy
-                // record-driven units get their carried state here (st_in may alias st_out; a unit that overflows
-                // returns before it writes any and is redone, state included, by the finish kernel)
-                r = w.run(st_in ? st_in + sj : nullptr, st_out ? st_out + sj : nullptr);
-                slow = w.overflow;  // does not fit the descriptor: redo this unit from its bytes
-            }
-            if (slow) {
-                r = stream_count_slow(tg, bytes, total, chunk_off + d0, d1 - d0, lane, flags, st_in ? st_in + sj : nullptr);
-                if (desc && lane == 0) desc[sj].nruns = -1;
-            }
+            const StreamResult r = stream_count_unit(tg, bytes, total, chunk_off + d0, d1 - d0, lane, flags, ts, st_in ? st_in + sj : nullptr,
+                                                     st_out ? st_out + sj : nullptr, desc ? desc + sj : nullptr);
             if (lane == j) tot = r.total_out;
             __syncwarp();
         }
@@ -1068,7 +1078,7 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
     TokSrc ts;
     UnitDesc* desc = (UnitDesc*)((uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req));
     uint8_t* tok_scratch = (uint8_t*)scratch + strip_general_scratch_bytes(n_resp, n_req) + desc_scratch_bytes(n_resp);
-    const int lane_steps = env_int("QB200_LANE_STEPS", 72);  // 0: warp per response only
+    const int lane_steps = env_int("QB200_LANE_STEPS", 40);  // longer responses go to the queue; 0: warp per response only
     const int path = path_choice();
     // words that must start at zero: the look-back words + ticket of request_offsets_kernel, then the run pool's counter
     // (they live in the `reqlen` part of the scratch; the tokenizer kernel clears them, else a memset)

@@ -555,7 +555,8 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
     for (int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib; r < n_resp; r += (int64_t)gridDim.x * kWarpsPerBlock) {
-        // (prefetching the next response's metadata lines here made the kernel slower: cfg3 1.12 -> 1.17 ms)
+        // (prefetching the next response's metadata lines here made the kernel slower: cfg3 1.12 -> 1.17 ms; so did loading
+        // all of a unit's metadata - offsets, destination, length, descriptor, runs - side by side up front: 1.38 ms)
         const int64_t a = in_off[r], b = in_off[r + 1];
         const int64_t de = dst[r];
         if (de < 0) {  // excluded from the join

@@ -1,29 +1,35 @@
-"""e2e (host buffers) time of the cfg2 stream feed against the number of pipeline slices (scratch measurement helper)."""
+"""e2e (host buffers) time of a workload against the number of pipeline slices (scratch measurement helper).
+usage: python tools/e2e_slices.py cfg3|cfg2 [slices ...]"""
+import os
 import sys
 import time
 
-import numpy as np
 import torch
 
-sys.path.insert(0, ".")
-import quorum_b200 as qb
-from quorum_b200 import synth
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
 
-dev = torch.device("cuda", 0)
-n = 65536
-base = synth.cfg2_base()
-idx = synth.gather_units(base, n, seed=1002)
-data = torch.from_numpy(np.ascontiguousarray(base[idx]).reshape(-1)).pin_memory()
-co = torch.arange(0, data.numel() + 1, 64, dtype=torch.int64).pin_memory()
-so = torch.arange(0, n * 256 + 1, 256, dtype=torch.int64).pin_memory()
-sess = qb.batch.HostStreamFeeder(qb.batch.tag_table(synth.TAGS5), dev, data.numel(), co.numel() - 1, n)
-for slices in (4, 8, 12, 16, 24, 32):
+wl = sys.argv[1] if len(sys.argv) > 1 else "cfg3"
+counts = [int(x) for x in sys.argv[2:]] or [12, 24, 48, 96]
+ctx = bench.Ctx()
+ctx.torch, ctx.dist, ctx.rank, ctx.world, ctx.dev = torch, None, 0, 1, torch.device("cuda", 0)
+W = bench.make_workload(ctx, wl, dict(bench.WORKLOADS[wl]))
+h_data = torch.empty(W.total_in, dtype=torch.uint8).pin_memory()
+h_data.copy_(W.data)
+h_a, h_b = W.host()
+sess = W.session()
+for slices in counts:
+    if W.wl["kind"] == "stream":
+        call = lambda: sess.run(h_data, h_a, h_b, flush=True, slices=slices)  # noqa: E731
+    else:
+        call = lambda: sess.run(h_data, h_a, h_b, hide=True, streaming=False, slices=slices)  # noqa: E731
     for _ in range(2):
-        sess.run(data, co, so, flush=True, slices=slices)
+        call()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(5):
-        sess.run(data, co, so, flush=True, slices=slices)
+        call()
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / 5
-    print(slices, round(dt * 1e3, 2), "ms", round(data.numel() / dt / 1e9, 1), "GB/s")
+    print(wl, "slices", slices, round(dt * 1e3, 2), "ms", round(W.total_in / dt / 1e9, 1), "GB/s")

@@ -195,6 +195,17 @@ int qb200_assemble_prompts_batch(const uint8_t *resp_bytes, const int64_t *resp_
  * [req_off[q], req_off[q+1]).  Device pointers. */
 int qb200_usage_sums_batch(const int64_t *usage, const int64_t *req_off, int64_t n_req, int64_t *out, void *stream);
 
+/* 32-bit lengths <-> 64-bit offsets on the device.  No counterpart in the reference (it has no buffers): the offset arrays of
+ * the two batch entry points are int64, which for 64-byte chunks is 11 % of what a host uploads and 20 % of what it reads
+ * back; a host can ship int32 lengths over PCIe instead and convert here.
+ *   qb200_offsets_from_lengths32: off[i + 1] = off[0] + len[0] + .. + len[i] for i < n; off[0] must already hold the start
+ *     (0 for a whole batch; for a slice of a larger batch the previous slice's call left it there).
+ *   qb200_lengths32_from_offsets: len[i] = off[i + 1] - off[i].
+ * Device pointers. */
+size_t qb200_offsets_scratch_bytes(int64_t n);
+int qb200_offsets_from_lengths32(const int32_t *len, int64_t n, int64_t *off, void *scratch, size_t scratch_bytes, void *stream);
+int qb200_lengths32_from_offsets(const int64_t *off, int64_t n, int32_t *len, void *stream);
+
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 int64_t qb200_launch_count(void);
 

@@ -19,6 +19,7 @@ EXPORTS = [
     "qb200_sse_frame_scratch_bytes", "qb200_sse_frame_batch", "qb200_profile_begin", "qb200_profile_end",
     "qb200_assemble_scratch_bytes", "qb200_assemble_prompts_batch", "qb200_usage_sums_batch",
     "qb200_sse_split_scratch_bytes", "qb200_sse_split_batch", "qb200_sse_parse_scratch_bytes", "qb200_sse_parse_batch",
+    "qb200_offsets_scratch_bytes", "qb200_offsets_from_lengths32", "qb200_lengths32_from_offsets",
 ]
 NOALLOC_MAX_STREAMS = 65536
 
@@ -63,6 +64,12 @@ def lib() -> ctypes.CDLL:
     L.qb200_assemble_scratch_bytes.argtypes = [i64, i64]
     L.qb200_assemble_prompts_batch.restype = ctypes.c_int
     L.qb200_assemble_prompts_batch.argtypes = [vp, vp, i64, vp, i64, vp, vp, vp, vp, i32, vp, i32, vp, i32, vp, i64, vp, vp, sz, vp]
+    L.qb200_offsets_scratch_bytes.restype = sz
+    L.qb200_offsets_scratch_bytes.argtypes = [i64]
+    L.qb200_offsets_from_lengths32.restype = ctypes.c_int
+    L.qb200_offsets_from_lengths32.argtypes = [vp, i64, vp, vp, sz, vp]
+    L.qb200_lengths32_from_offsets.restype = ctypes.c_int
+    L.qb200_lengths32_from_offsets.argtypes = [vp, i64, vp, vp]
     L.qb200_usage_sums_batch.restype = ctypes.c_int
     L.qb200_usage_sums_batch.argtypes = [vp, vp, i64, vp, vp]
     L.qb200_sse_split_scratch_bytes.restype = sz

@@ -204,6 +204,19 @@ def stream_flush_batch(state: torch.Tensor) -> torch.Tensor:
     return state
 
 
+def offsets_from_lengths32(lengths: torch.Tensor, off: torch.Tensor, scratch: torch.Tensor) -> None:
+    """off[i + 1] = off[0] + lengths[0] + .. + lengths[i] on the device (qb200_offsets_from_lengths32); off[0] must hold the start."""
+    n = lengths.numel()
+    with torch.cuda.device(off.device):
+        check(lib().qb200_offsets_from_lengths32(_ptr(lengths), n, _ptr(off), _ptr(scratch), scratch.numel(), _stream_ptr(off.device)))
+
+
+def lengths32_from_offsets(off: torch.Tensor, lengths: torch.Tensor) -> None:
+    """lengths[i] = off[i + 1] - off[i] as int32 on the device (qb200_lengths32_from_offsets)."""
+    with torch.cuda.device(off.device):
+        check(lib().qb200_lengths32_from_offsets(_ptr(off), lengths.numel(), _ptr(lengths), _stream_ptr(off.device)))
+
+
 # ---- host <-> device packing helpers -----------------------------------------------------------------------------
 
 def pack_host(items: Sequence[bytes]) -> Tuple[torch.Tensor, torch.Tensor]:
@@ -315,6 +328,85 @@ class HostStreamFeeder:
         cur.wait_stream(s_out)
         total = int(self.h_oco[nc])
         return nb + 8 * (nc + 1) + 8 * (ns + 1), total + 8 * (nc + 1)
+
+
+    def run_compact(self, h_data: torch.Tensor, h_chunk_len: torch.Tensor, h_stream_off: torch.Tensor,
+                    h_stream_byte_off: torch.Tensor, *, flush: bool, carry_state: bool = False, slices: Optional[int] = None):
+        """run() with 32-bit per-chunk LENGTHS over PCIe instead of 64-bit offsets, both ways: for 64-byte chunks the int64
+        offset arrays are 11 % of the upload and 20 % of the download.  h_chunk_len int32[n_chunks]; h_stream_off
+        int64[n_streams + 1] (chunk indices); h_stream_byte_off int64[n_streams + 1] (byte offset of every stream's first
+        chunk, last entry = total bytes).  The offsets the kernels need are built on the device
+        (qb200_offsets_from_lengths32) and the per-chunk output lengths are narrowed there (qb200_lengths32_from_offsets).
+        Returns (h2d_bytes, d2h_bytes); results: self.h_out[:total] and self.h_olen[:n_chunks] (int32 length of every
+        feed's return value), total = self.h_ends[-1] of the call."""
+        nb, nc, ns = h_data.numel(), h_chunk_len.numel(), h_stream_off.numel() - 1
+        if slices is None:
+            slices = default_slices(nb)
+        if ns < 4 * slices or nb < (1 << 22):
+            slices = 1
+        dev = self.dev
+        cur = torch.cuda.current_stream(dev)
+        if not hasattr(self, "_s_in"):
+            self._s_in, self._s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        if not hasattr(self, "d_len"):
+            mc = self.d_co.numel() - 1
+            self.d_len = torch.empty(mc, dtype=torch.int32, device=dev)
+            self.d_olen = torch.empty(mc, dtype=torch.int32, device=dev)
+            self.h_olen = torch.empty(mc, dtype=torch.int32).pin_memory()
+            self.d_cscratch = torch.empty(lib().qb200_offsets_scratch_bytes(mc), dtype=torch.uint8, device=dev)
+            self.h_ends_buf = torch.zeros(257, dtype=torch.int64).pin_memory()
+        s_in, s_out = self._s_in, self._s_out
+        s_in.wait_stream(cur)
+        s_out.wait_stream(cur)
+        d_data, d_co, d_so, d_oco = self.d_data[:nb], self.d_co[:nc + 1], self.d_so[:ns + 1], self.d_oco[:nc + 1]
+        slices = min(slices, 256)
+        h_ends = self.h_ends_buf[:slices + 1]
+        h_ends[0] = 0
+        with torch.cuda.stream(s_in):
+            d_so.copy_(h_stream_off, non_blocking=True)
+            d_co[nc:nc + 1].copy_(h_stream_byte_off[ns:ns + 1], non_blocking=True)   # the kernels bound their reads by chunk_off[n_chunks]
+            d_co[0:1].zero_()
+        sb = [ns * k // slices for k in range(slices + 1)]                      # stream bounds
+        cb = [int(h_stream_off[i]) for i in sb]                                # chunk bounds (host reads, pinned)
+        bb = [int(h_stream_byte_off[i]) for i in sb]                           # byte bounds
+        ev_o, pending = [], None
+
+        def drain(k):                                                          # slice k's bytes -> host, once its end is known
+            ev_o[k].synchronize()
+            o0, o1 = int(h_ends[k]), int(h_ends[k + 1])
+            with torch.cuda.stream(s_out):
+                self.h_out[o0:o1].copy_(self.d_out[o0:o1], non_blocking=True)
+
+        for k in range(slices):
+            with torch.cuda.stream(s_in):
+                d_data[bb[k]:bb[k + 1]].copy_(h_data[bb[k]:bb[k + 1]], non_blocking=True)
+                self.d_len[cb[k]:cb[k + 1]].copy_(h_chunk_len[cb[k]:cb[k + 1]], non_blocking=True)
+                ev_in = torch.cuda.Event()
+                ev_in.record(s_in)
+            cur.wait_event(ev_in)
+            offsets_from_lengths32(self.d_len[cb[k]:cb[k + 1]], d_co[cb[k]:], self.d_cscratch)   # continues from d_co[cb[k]]
+            st = self.d_state[sb[k]:sb[k + 1]]
+            stream_feed_batch(self.tags, d_data, d_co, d_so[sb[k]:sb[k + 1] + 1], st if carry_state else None, flush=flush,
+                              state_out=st, out_bytes=self.d_out, out_chunk_off=d_oco, scratch=self.d_scratch, chain=k > 0)
+            lengths32_from_offsets(d_oco[cb[k]:], self.d_olen[cb[k]:cb[k + 1]])
+            ev_c = torch.cuda.Event()
+            ev_c.record(cur)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_c)
+                self.h_olen[cb[k]:cb[k + 1]].copy_(self.d_olen[cb[k]:cb[k + 1]], non_blocking=True)
+                h_ends[k + 1:k + 2].copy_(d_oco[cb[k + 1]:cb[k + 1] + 1], non_blocking=True)
+                e = torch.cuda.Event()
+                e.record(s_out)
+                ev_o.append(e)
+            if pending is not None:
+                drain(pending)
+            pending = k
+        drain(pending)
+        s_out.synchronize()
+        cur.wait_stream(s_out)
+        self.h_ends = h_ends
+        total = int(h_ends[slices])
+        return nb + 4 * nc + 16 * (ns + 1), total + 4 * nc + 8 * slices
 
 
 class HostStripConcat:

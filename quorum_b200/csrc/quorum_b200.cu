@@ -839,6 +839,15 @@ __global__ void stream_flush_kernel(StreamState* st, int64_t n) {
 
 __global__ void set_i64_kernel(int64_t* p, int64_t v) { *p = v; }
 
+// 32-bit lengths <-> 64-bit offsets (what a host ships over PCIe instead of 8 bytes per chunk)
+__global__ void widen_i32_kernel(const int32_t* __restrict__ v, int64_t n, int64_t* __restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = v[i];
+}
+__global__ void lengths_i32_kernel(const int64_t* __restrict__ off, int64_t n, int32_t* __restrict__ len) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        len[i] = (int32_t)(off[i + 1] - off[i]);
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------------------------------------------
@@ -1453,6 +1462,39 @@ int qb200_assemble_prompts_batch(const uint8_t* resp_bytes, const int64_t* resp_
                                                                   n_labels, sep, sep_len, out_off, out_bytes);
         LAUNCHED("assemble_copy_kernel");
     }
+    CUDA_TRY(cudaGetLastError());
+    return QB200_OK;
+}
+
+size_t qb200_offsets_scratch_bytes(int64_t n) {
+    if (n < 0) n = 0;
+    return align256((size_t)(n + 2) * 8) + align256((size_t)(n / kScanSlice + 4) * 8) + 256;
+}
+
+int qb200_offsets_from_lengths32(const int32_t* len, int64_t n, int64_t* off, void* scratch, size_t scratch_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (n < 0 || !off || (n > 0 && !len)) return fail(QB200_EINVAL, "offsets_from_lengths32: bad argument");
+    if (n == 0) return QB200_OK;
+    if (scratch_bytes < qb200_offsets_scratch_bytes(n) || !scratch) return fail(QB200_ESCRATCH, "offsets_from_lengths32: scratch too small");
+    int64_t* wide = (int64_t*)scratch;
+    int64_t* partial = (int64_t*)((uint8_t*)scratch + align256((size_t)(n + 2) * 8));
+    int64_t g = (n + 255) / 256;
+    if (g > 148 * 16) g = 148 * 16;
+    widen_i32_kernel<<<(unsigned)g, 256, 0, stream>>>(len, n, wide);
+    LAUNCHED("widen_i32_kernel");
+    launch_scan(wide, n, off, partial, stream, off, nullptr);  // continues from the value already in off[0]
+    CUDA_TRY(cudaGetLastError());
+    return QB200_OK;
+}
+
+int qb200_lengths32_from_offsets(const int64_t* off, int64_t n, int32_t* len, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (n < 0 || (n > 0 && (!off || !len))) return fail(QB200_EINVAL, "lengths32_from_offsets: bad argument");
+    if (n == 0) return QB200_OK;
+    int64_t g = (n + 255) / 256;
+    if (g > 148 * 16) g = 148 * 16;
+    lengths_i32_kernel<<<(unsigned)g, 256, 0, stream>>>(off, n, len);
+    LAUNCHED("lengths_i32_kernel");
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;
 }

@@ -203,6 +203,39 @@ def test_chained_slices_and_pipelined_host_feeder(qb, path_env, path):
         assert np.array_equal(st["depth"], exp_st["depth"]) and np.array_equal(st["held_len"], exp_st["held_len"])
 
 
+def test_compact_host_feeder_32bit_lengths(qb):
+    """run_compact: int32 chunk lengths up, int32 output lengths down, offsets built and narrowed on the device
+    (qb200_offsets_from_lengths32 / qb200_lengths32_from_offsets).  Ragged chunks (empty ones included), several slice
+    counts; bytes, per-chunk lengths and carried state equal the oracle's."""
+    from oracle import c_oracle
+    from quorum_b200 import synth
+    dev = torch.device("cuda", 0)
+    base = synth.cfg2_base(64)
+    idx = synth.gather_units(base, 640, seed=9)
+    data = np.ascontiguousarray(base[idx]).reshape(-1)
+    per = data.size // 640
+    rng = np.random.default_rng(12)
+    cuts = np.sort(rng.integers(0, per + 1, size=(640, 255)), axis=1)
+    bounds = np.concatenate([np.zeros((640, 1), np.int64), cuts, np.full((640, 1), per, np.int64)], axis=1) + (np.arange(640) * per)[:, None]
+    chunk_len = np.diff(bounds, axis=1).astype(np.int32).reshape(-1)
+    chunk_off = np.concatenate([[0], np.cumsum(chunk_len, dtype=np.int64)])
+    stream_off = np.arange(0, 640 * 256 + 1, 256, dtype=np.int64)
+    stream_byte_off = np.arange(0, 641, dtype=np.int64) * per
+    exp_out, exp_oco, exp_st = c_oracle.stream_feed_batch(c_oracle.Tags(synth.TAGS5), data, chunk_off, stream_off, None, 0)
+    feeder = qb.batch.HostStreamFeeder(qb.batch.tag_table(synth.TAGS5), dev, data.size, len(chunk_len), 640)
+    pin = lambda a: torch.from_numpy(np.array(a, copy=True)).pin_memory()  # noqa: E731
+    for slices in (1, 5, 8):
+        feeder.h_out.zero_()
+        h2d, d2h = feeder.run_compact(pin(data), pin(chunk_len), pin(stream_off), pin(stream_byte_off), flush=False, slices=slices)
+        torch.cuda.synchronize()
+        assert int(feeder.h_ends[-1]) == int(exp_oco[-1]), slices
+        assert np.array_equal(feeder.h_olen[: len(chunk_len)].numpy(), np.diff(exp_oco).astype(np.int32)), slices
+        assert np.array_equal(feeder.h_out[: int(exp_oco[-1])].numpy(), exp_out), slices
+        st = feeder.d_state[:640].cpu().numpy().reshape(-1).view(c_oracle.STATE_DTYPE)
+        assert np.array_equal(st["depth"], exp_st["depth"]) and np.array_equal(st["held_len"], exp_st["held_len"])
+        assert h2d < data.size + 8 * len(chunk_off) and d2h < int(exp_oco[-1]) + 8 * len(chunk_off)
+
+
 def test_chained_slices_and_pipelined_host_strip_concat(qb):
     """QB200_CHAIN on strip + concat: the host-buffer session processes the batch in slices of requests on three streams;
     bytes and request offsets equal those of one call (ragged requests, multi-byte separator, both join forms)."""

@@ -17,10 +17,17 @@ ctx.torch, ctx.dist, ctx.rank, ctx.world, ctx.dev = torch, None, 0, 1, torch.dev
 W = bench.make_workload(ctx, wl, dict(bench.WORKLOADS[wl]))
 h_data = torch.empty(W.total_in, dtype=torch.uint8).pin_memory()
 h_data.copy_(W.data)
-h_a, h_b = W.host()
 sess = W.session()
+compact = os.environ.get("E2E_COMPACT") == "1" and W.wl["kind"] == "stream"
+if W.wl["kind"] == "stream":                 # compact: int32 chunk lengths + per-stream byte offsets; else int64 chunk offsets
+    h_len, h_b, h_sbo = W.host()
+    h_a = torch.cat([torch.zeros(1, dtype=torch.int64), torch.cumsum(h_len.to(torch.int64), 0)]).pin_memory()
+else:
+    h_a, h_b = W.host()
 for slices in counts:
-    if W.wl["kind"] == "stream":
+    if compact:
+        call = lambda: sess.run_compact(h_data, h_len, h_b, h_sbo, flush=True, slices=slices)  # noqa: E731
+    elif W.wl["kind"] == "stream":
         call = lambda: sess.run(h_data, h_a, h_b, flush=True, slices=slices)  # noqa: E731
     else:
         call = lambda: sess.run(h_data, h_a, h_b, hide=True, streaming=False, slices=slices)  # noqa: E731
@@ -32,4 +39,4 @@ for slices in counts:
         call()
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / 5
-    print(wl, "slices", slices, round(dt * 1e3, 2), "ms", round(W.total_in / dt / 1e9, 1), "GB/s")
+    print(wl, "compact" if compact else "int64", "slices", slices, round(dt * 1e3, 2), "ms", round(W.total_in / dt / 1e9, 1), "GB/s")

@@ -128,6 +128,9 @@ __device__ int64_t match_tag(const DevTags& tg, const A& B, int64_t x, int64_t e
 // open and close tags together: returns the tag length in bytes (0 = not a tag); is_close, cls, exrel (offset of the
 // first U+0130/U+0131/U+017F form, 0xFF if none) as in match_tag.  ASCII spellings take the word-compare path; anything
 // with a non-ASCII byte in the window falls back to the exact byte-wise matcher.
+// kDefer: a window that needs the exact matcher returns -1 instead of running it (the tokenizer collects such candidates
+// and matches them 32 at a time).
+template <bool kDefer = false>
 __device__ __forceinline__ int fast_match_tag(const DevTags& tg, const uint8_t* D, int x, int end, int& is_close, int& cls,
                                               int& exrel) {
     is_close = 0;
@@ -175,6 +178,7 @@ __device__ __forceinline__ int fast_match_tag(const DevTags& tg, const uint8_t* 
     };
     if (((b0 | b1 | b2 | b3 | b4 | b5) & 0x80808080u) &&
         (fold_lead(b0, b1) | fold_lead(b1, b2) | fold_lead(b2, b3) | fold_lead(b3, b4) | fold_lead(b4, b5) | fold_lead(b5, 0x84848484u))) {
+        if (kDefer) return -1;
         const PtrAcc A{D};
         int64_t ex;
         int64_t tend = match_tag(tg, A, x, end, is_close != 0, cls, ex);

@@ -9,6 +9,8 @@
 namespace qb {
 
 // Exact tag test at x for a flat global buffer: word-compare fast path when the longest possible tag (69 bytes) is readable, else byte-wise.
+// Returns -1 when the window holds a lead byte of a fold form (U+0130/0131/017F/212A): the caller defers it (TokDefer).
+template <bool kDefer>
 __device__ __forceinline__ int tag_at(const DevTags& tg, const uint8_t* buf, int64_t total, int64_t x, int& is_close, int& cls,
                                       int& exotic) {
     exotic = 0;
@@ -16,7 +18,7 @@ __device__ __forceinline__ int tag_at(const DevTags& tg, const uint8_t* buf, int
         int exrel;
         // fast_match_tag indexes with int: rebase so that the candidate sits at a small offset
         const int64_t base = x & ~(int64_t)3;
-        const int len = fast_match_tag(tg, buf + base, (int)(x - base), 1 << 30, is_close, cls, exrel);
+        const int len = fast_match_tag<kDefer>(tg, buf + base, (int)(x - base), 1 << 30, is_close, cls, exrel);  // -1: deferred
         exotic = exrel != 0xFF;
         return len;
     }
@@ -37,9 +39,53 @@ __device__ __forceinline__ uint32_t lt_any16(const uint4& v) { return lt_any(v.x
 
 // Per-warp scratch of the tokenizer (shared memory): the candidate list of a dense pair.
 constexpr int kTokList = 2 * kRecPerStep;
-struct TokWarpScratch {
+constexpr int kTokDefer = 32 + 2 * kRecPerStep;
+struct __align__(8) TokWarpScratch {
+    int64_t dpos[kTokDefer];   // deferred candidates (need the exact byte matcher): absolute position ...
+    uint8_t drank[kTokDefer];  // ... and rank inside its step (= record slot)
+    int ndef;                  // entries waiting in dpos / drank
     uint16_t list[kTokList];   // positions (inside the 2 KiB pair) of the '<' candidates, in position order
 };
+
+__device__ __forceinline__ uint32_t pack_rec(int pos, int len, int is_close, int cls, int exotic) {
+    return (uint32_t)pos | ((uint32_t)len << 10) | ((len ? (uint32_t)is_close : 2u) << 17) | ((uint32_t)cls << 19) | ((uint32_t)exotic << 26);
+}
+
+// The exact matcher for deferred candidates [first, first + n) of the warp's list, one per lane: fold spellings are rare
+// in text and frequent in adversarial text, and the byte-wise matcher costs ~10x the word compare, so it pays to run it
+// with all lanes busy instead of under the divergence of the pair it came from (cfg5: 8 of 32 lanes active before).
+__device__ __forceinline__ void tok_drain(const DevTags& tg, const uint8_t* __restrict__ bytes, int64_t total, uint32_t* __restrict__ rec,
+                                       const TokWarpScratch& W, int first, int n, int lane) {
+    if (lane < n) {
+        const int64_t x = W.dpos[first + lane];
+        const PtrAcc A{bytes};
+        const int is_close = bytes[x + 1] == '/';
+        int cls = 0;
+        int64_t ex;
+        const int64_t tend = match_tag(tg, A, x, total, is_close != 0, cls, ex);
+        const int len = tend >= 0 ? (int)(tend - x) : 0;
+        rec[(x >> 10) * kRecPerStep + W.drank[first + lane]] = pack_rec((int)(x & 1023), len, is_close, len ? cls : 0, len && ex >= 0);
+    }
+}
+
+// Warp-collective: lanes with `need` append (x, rank) to the warp's deferred list (counter in shared memory: the pairs of
+// ordinary text never come here and pay no register for it).  The list is drained between pairs (tokenize_kernel), so
+// it holds at most 31 + 2 * kRecPerStep entries.
+__device__ __forceinline__ bool tok_defer(TokWarpScratch& W, bool need, int64_t x, int rank, int lane) {
+    const unsigned m = __ballot_sync(kFull, need);
+    if (m) {
+        const int nd = W.ndef;
+        __syncwarp();
+        if (need) {
+            const int k = nd + __popc(m & ((1u << lane) - 1u));
+            W.dpos[k] = x;
+            W.drank[k] = (uint8_t)rank;
+        }
+        if (lane == 0) W.ndef = nd + __popc(m);
+        __syncwarp();
+    }
+    return m != 0;
+}
 
 // One 2 KiB pair of steps `pr` of the flat buffer, by one warp: lane j loads bytes [64j, 64j+64) with four 16-byte loads
 // (lanes 0-15 read the first step, lanes 16-31 the second), so one ballot and one divergent "look at the candidates"
@@ -50,11 +96,14 @@ struct TokWarpScratch {
 //     per-lane counts) and matched ONE PER LANE, so the expensive part (tag_at) runs once per 32 candidates instead of
 //     once per candidate of the busiest lane (adversarial text has 40 '<' per KiB in places: cfg5's tokenizer 1.16 ->
 //     0.65 ms); a candidate's record goes straight to its slot: its rank inside its step is its list index minus the
-//     step's first index.
+//     step's first index.  Candidates whose window holds a fold-form lead byte need the exact byte-wise matcher: they are
+//     deferred to the warp's list (tok_defer) and matched 32 at a time between pairs (tok_drain): cfg5 0.69 -> 0.50 ms.
+//     The sparse path does not defer: the extra ballot there cost cfg2's tokenizer 2.7 % for 5 % more on cfg5.
+// Returns true when something was deferred.
 // cnt / rec are indexed by absolute step (the caller may pass pointers shifted so that the steps of a tile land in shared
 // memory); steps >= nsteps are not written, bytes at and beyond `total` are never read.  A step with more than
 // kRecPerStep candidates gets cnt = kRecOverflow and no records.
-__device__ __forceinline__ void tokenize_pair(const DevTags& tg, const uint8_t* __restrict__ bytes, int64_t total, int64_t nsteps,
+__device__ __forceinline__ bool tokenize_pair(const DevTags& tg, const uint8_t* __restrict__ bytes, int64_t total, int64_t nsteps,
                                               int64_t pr, int lane, uint8_t* cnt, uint32_t* rec, TokWarpScratch& W) {
     const int half = lane >> 4;
     const unsigned hm = half ? 0xFFFF0000u : 0x0000FFFFu;  // the lanes of this lane's step
@@ -82,21 +131,23 @@ __device__ __forceinline__ void tokenize_pair(const DevTags& tg, const uint8_t* 
     const int64_t step = (pr << 1) + half;
     if (any == 0) {  // the common case: no '<' in these 2 KiB
         if ((lane & 15) == 0 && step < nsteps) cnt[step] = 0;
-        return;
+        return false;
     }
     const int nr = __popc(lt0) + __popc(lt1);
     if (__all_sync(kFull, nr <= 1)) {  // sparse: one record per lane at most, ranks straight from the ballot
         const int tot = __popc(any & hm);
-        if (nr) {
-            const int b = lt0 ? __ffs(lt0) - 1 : 32 + __ffs(lt1) - 1;
+        bool need = false;
+        int b = 0;
+        const int rank = __popc(any & hm & (0xffffffffu >> (31 - lane))) - 1;
+        if (nr && step < nsteps) {
+            b = lt0 ? __ffs(lt0) - 1 : 32 + __ffs(lt1) - 1;
             int is_close, cls, exotic;
-            const int len = tag_at(tg, bytes, total, a + b, is_close, cls, exotic);
-            const uint32_t r = (uint32_t)((lane & 15) * 64 + b) | ((uint32_t)len << 10) | ((len ? (uint32_t)is_close : 2u) << 17) |
-                               ((uint32_t)cls << 19) | ((uint32_t)exotic << 26);
-            if (step < nsteps) rec[step * kRecPerStep + __popc(any & hm & (0xffffffffu >> (31 - lane))) - 1] = r;
+            const int len = tag_at<false>(tg, bytes, total, a + b, is_close, cls, exotic);
+            need = false;
+            if (!need) rec[step * kRecPerStep + rank] = pack_rec((lane & 15) * 64 + b, len, is_close, cls, exotic);
         }
         if ((lane & 15) == 0 && step < nsteps) cnt[step] = (uint8_t)tot;  // at most 16
-        return;
+        return false;
     }
     // dense: ranks from a warp scan, candidates compacted into the list, one per lane per round
     int incl = nr;
@@ -122,18 +173,30 @@ __device__ __forceinline__ void tokenize_pair(const DevTags& tg, const uint8_t* 
         }
     }
     __syncwarp();
-    for (int i = lane; i < n_list; i += 32) {
-        const int pos = W.list[i];
-        const int sl = pos >> 10;
-        int is_close, cls, exotic;
-        const int len = tag_at(tg, bytes, total, (pr << 11) + pos, is_close, cls, exotic);
-        const uint32_t r = (uint32_t)(pos & 1023) | ((uint32_t)len << 10) | ((len ? (uint32_t)is_close : 2u) << 17) |
-                           ((uint32_t)cls << 19) | ((uint32_t)exotic << 26);
-        const int64_t st = (pr << 1) + sl;
-        if (st < nsteps) rec[st * kRecPerStep + (i - (sl ? first1 : 0))] = r;
+    bool deferred = false;
+    for (int i0 = 0; i0 < n_list; i0 += 32) {
+        const int i = i0 + lane;
+        bool need = false;
+        int64_t x = 0;
+        int rank = 0;
+        if (i < n_list) {
+            const int pos = W.list[i];
+            const int sl = pos >> 10;
+            const int64_t st = (pr << 1) + sl;
+            if (st < nsteps) {
+                int is_close, cls, exotic;
+                x = (pr << 11) + pos;
+                const int len = tag_at<true>(tg, bytes, total, x, is_close, cls, exotic);
+                rank = i - (sl ? first1 : 0);
+                need = len < 0;
+                if (!need) rec[st * kRecPerStep + rank] = pack_rec(pos & 1023, len, is_close, cls, exotic);
+            }
+        }
+        deferred |= tok_defer(W, need, x, rank, lane);
     }
     if ((lane & 15) == 0 && step < nsteps) cnt[step] = (uint8_t)((half ? bad1 : bad0) ? kRecOverflow : (half ? c1 : c0));
     __syncwarp();
+    return deferred;
 }
 
 // The byte range to tokenize is [off[idx ? idx[0] : 0], off[idx ? idx[n] : n)): the units of this call (a chained call
@@ -153,13 +216,27 @@ __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant_
     if (nsteps > max_steps) nsteps = max_steps;
     const int64_t npairs = (nsteps + 1) >> 1;
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    TokWarpScratch& W = s_tok[threadIdx.x >> 5];
+    if (lane == 0) W.ndef = 0;
+    __syncwarp();
     for (int64_t pr = (begin >> 11) + (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); pr < npairs; pr += nwarps) {
         {   // this warp's next 2 KiB: get its sixteen lines into L2 now, one iteration of work ahead of their use
             const int64_t an = ((pr + nwarps) << 11) + lane * 128;
             if (lane < 16 && an + 128 <= total) asm volatile("prefetch.global.L2 [%0];" ::"l"(bytes + an));
         }
-        tokenize_pair(tg, bytes, total, nsteps, pr, lane, cnt, rec, s_tok[threadIdx.x >> 5]);
+        if (!tokenize_pair(tg, bytes, total, nsteps, pr, lane, cnt, rec, W)) continue;
+        int nd = W.ndef;
+        if (nd >= 32) {  // full warps' worth of deferred candidates
+            do {
+                nd -= 32;
+                tok_drain(tg, bytes, total, rec, W, nd, 32, lane);
+            } while (nd >= 32);
+            __syncwarp();
+            if (lane == 0) W.ndef = nd;
+            __syncwarp();
+        }
     }
+    if (W.ndef) tok_drain(tg, bytes, total, rec, W, 0, W.ndef, lane);
 }
 
 }  // namespace qb

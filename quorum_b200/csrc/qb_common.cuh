@@ -372,6 +372,8 @@ __device__ __forceinline__ uint4 realign_w(const uint4& A, const uint4& B, int s
     o.w = __funnelshift_r(w3, w4, sh);
     return o;
 }
+// (four vectors per lane per round with the neighbour's words taken by shuffle instead of the second load: cfg3's copy
+// 1.08 -> 1.57 ms)
 template <int W>
 __device__ __forceinline__ void copy_vecs_w(uint4* __restrict__ d4, const uint4* __restrict__ s4, int nvec, int sh, int lane) {
     int v = lane;
@@ -385,11 +387,16 @@ __device__ __forceinline__ void copy_vecs_w(uint4* __restrict__ d4, const uint4*
         d4[v] = realign_w<W>(a0, b0, sh);
     }
 }
+// The bytes in front of the first aligned 16-byte store and behind the last one are loaded before the vectors and stored
+// after them, so that a run costs one memory round trip, not three (a store waits for its load, and nothing issues past
+// a waiting store: with ~400-byte runs the three dependent steps were most of cfg5's copy time).
 __device__ __forceinline__ void warp_copy_fast(uint8_t* dst, const uint8_t* src, int n, const uint8_t* src_hi, int lane) {
     if (n <= 0) return;
     int head = (int)((16u - (uint32_t)reinterpret_cast<uintptr_t>(dst)) & 15u);
     if (head > n) head = n;
-    if (lane < head) dst[lane] = src[lane];
+    uint8_t hb = 0, tb = 0;
+    if (lane < head) hb = src[lane];
+    uint8_t* const dst0 = dst;
     dst += head;
     src += head;
     n -= head;
@@ -397,6 +404,13 @@ __device__ __forceinline__ void warp_copy_fast(uint8_t* dst, const uint8_t* src,
     const uint4* s4 = reinterpret_cast<const uint4*>(src - shift);
     uint4* d4 = reinterpret_cast<uint4*>(dst);
     int nvec = n >> 4;
+    if (shift) {
+        // the realigning read touches the next 16-byte vector: keep that inside [.., src_hi)
+        const int64_t room = (src_hi - reinterpret_cast<const uint8_t*>(s4)) >> 4;  // whole vectors readable
+        if ((int64_t)nvec + 1 > room) nvec = room > 0 ? (int)(room - 1) : 0;
+    }
+    const int t0 = (nvec << 4) + lane;  // this lane's first byte behind the vectors
+    if (t0 < n) tb = src[t0];
     if (shift == 0) {
         int v = lane;
         for (; v + 32 < nvec; v += 64) {
@@ -406,9 +420,6 @@ __device__ __forceinline__ void warp_copy_fast(uint8_t* dst, const uint8_t* src,
         }
         if (v < nvec) d4[v] = s4[v];
     } else {
-        // the realigning read touches the next 16-byte vector: keep that inside [.., src_hi)
-        const int64_t room = (src_hi - reinterpret_cast<const uint8_t*>(s4)) >> 4;  // whole vectors readable
-        if ((int64_t)nvec + 1 > room) nvec = room > 0 ? (int)(room - 1) : 0;
         const int sh = (shift & 3) * 8;
         switch (shift >> 2) {
             case 0: copy_vecs_w<0>(d4, s4, nvec, sh, lane); break;
@@ -417,7 +428,9 @@ __device__ __forceinline__ void warp_copy_fast(uint8_t* dst, const uint8_t* src,
             default: copy_vecs_w<3>(d4, s4, nvec, sh, lane); break;
         }
     }
-    for (int i = (nvec << 4) + lane; i < n; i += 32) dst[i] = src[i];
+    if (lane < head) dst0[lane] = hb;
+    if (t0 < n) dst[t0] = tb;
+    for (int i = t0 + 32; i < n; i += 32) dst[i] = src[i];  // only when the vectors were cut short at the end of the buffer
 }
 
 }  // namespace qb

@@ -141,11 +141,11 @@ __device__ __forceinline__ bool stream_walk_lane(const DevTags& tg, const uint8_
           if (cpack == 0) continue;
 #pragma unroll
           for (int i = 0; i < 8; i++)
-              if ((cpack >> (8 * i)) & 0xFF) asm volatile("prefetch.global.L1 [%0];" ::"l"(ts.rec + (s0 + i) * kRecPerStep));
+              if ((cpack >> (8 * i)) & 0xFF) asm volatile("prefetch.global.L1 [%0];" ::"l"(ts.head(s0 + i)));
           // One loop over this lane's records of the eight steps, whatever step each is in: the lanes of a warp then
           // iterate max-over-lanes(records) times, not sum-over-steps(max-over-lanes(records in the step)).
           unsigned long long rest = cpack;
-          const uint32_t* rp = nullptr;
+          const uint32_t *rp = nullptr, *rp2 = nullptr;
           int cnt = 0, q = 0, sb = 0;
           for (;;) {
                 if (q == cnt) {  // next step of the eight that has records
@@ -155,10 +155,12 @@ __device__ __forceinline__ bool stream_walk_lane(const DevTags& tg, const uint8_
                     rest &= ~(0xFFull << (8 * i));
                     if (cnt == kRecOverflow) return false;
                     const int64_t sj = s0 + i;
-                    rp = ts.rec + sj * kRecPerStep;
+                    rp = ts.head(sj);
+                    rp2 = ts.tail(sj);
                     sb = (int)((sj << 10) - ustart);  // unit position of the step's first byte
                     q = 0;
                 }
+                if (q == kRecInline) rp = rp2;  // the step's records beyond the first eight live in the second array
                 const uint32_t r = rp[q++];
                 const int kind = (r >> 17) & 3;
                 const int x = sb + (int)(r & 1023);
@@ -281,15 +283,16 @@ __device__ __forceinline__ bool for_each_record(const TokSrc& ts, int64_t s_firs
         if (cpack == 0) continue;
 #pragma unroll
         for (int i = 0; i < 8; i++)
-            if ((cpack >> (8 * i)) & 0xFF) asm volatile("prefetch.global.L1 [%0];" ::"l"(ts.rec + (s0 + i) * kRecPerStep));
+            if ((cpack >> (8 * i)) & 0xFF) asm volatile("prefetch.global.L1 [%0];" ::"l"(ts.head(s0 + i)));
         for (int i = 0; i < 8; i++) {
             const int cnt = (int)((cpack >> (8 * i)) & 0xFF);
             if (cnt == 0) continue;
             if (cnt == kRecOverflow) return false;
             const int64_t sj = s0 + i;
-            const uint32_t* rp = ts.rec + sj * kRecPerStep;
+            const uint32_t* rp = ts.head(sj);
             const int sb = (int)((sj << 10) - ustart);
             for (int q = 0; q < cnt; q++) {
+                if (q == kRecInline) rp = ts.tail(sj);
                 const uint32_t r = rp[q];
                 f(r, sb + (int)(r & 1023));
             }

@@ -89,9 +89,10 @@ __device__ __noinline__ bool strip_scan_walk(const DevTags& tg, const uint8_t* b
             bad = true;
             continue;
         }
-        const uint32_t* rp = ts.rec + sj * kRecPerStep;
+        const uint32_t* rp = ts.head(sj);
         const int sb = (int)((sj << 10) - ustart);
         for (int q = 0; q < cnt; q++) {
+            if (q == kRecInline) rp = ts.tail(sj);
             const uint32_t r = rp[q];
             const int kind = (r >> 17) & 3;
             const int x = sb + (int)(r & 1023);
@@ -134,12 +135,13 @@ __device__ __noinline__ bool strip_scan_walk(const DevTags& tg, const uint8_t* b
         const int64_t sj = S0 + lane;
         const int cnt = sj <= s_last ? ts.count(sj) : 0;
         if (!__any_sync(kFull, cnt > 0)) continue;  // 32 steps without a '<': every vector is the identity, the state carries
-        const uint32_t* rp = ts.rec + sj * kRecPerStep;
+        const uint32_t *rh = ts.head(sj), *rt = ts.tail(sj);
+        auto recq = [&](int q) { return q < kRecInline ? rh[q] : rt[q]; };
         const int sb = (int)((sj << 10) - ustart);
         // B: this step's transition vector
         TVec v = tvec_identity();
         for (int q = 0; q < cnt; q++) {
-            const uint32_t r = rp[q];
+            const uint32_t r = recq(q);
             const int kind = (r >> 17) & 3;
             const int x = sb + (int)(r & 1023);
             if (kind == 2 || x < 0 || x + (int)((r >> 10) & 127) > n) continue;
@@ -165,7 +167,7 @@ __device__ __noinline__ bool strip_scan_walk(const DevTags& tg, const uint8_t* b
         {
             int st = state;
             for (int q = 0; q < cnt; q++) {
-                const uint32_t r = rp[q];
+                const uint32_t r = recq(q);
                 const int kind = (r >> 17) & 3;
                 const int x = sb + (int)(r & 1023);
                 if (kind == 2 || x < 0 || x + (int)((r >> 10) & 127) > n) continue;
@@ -194,7 +196,7 @@ __device__ __noinline__ bool strip_scan_walk(const DevTags& tg, const uint8_t* b
         {
             int st = state;
             for (int q = 0; q < cnt; q++) {
-                const uint32_t r = rp[q];
+                const uint32_t r = recq(q);
                 const int kind = (r >> 17) & 3;
                 const int x = sb + (int)(r & 1023);
                 const int tend = x + (int)((r >> 10) & 127);

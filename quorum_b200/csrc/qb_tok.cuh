@@ -47,6 +47,11 @@ struct __align__(8) TokWarpScratch {
     uint16_t list[kTokList];   // positions (inside the 2 KiB pair) of the '<' candidates, in position order
 };
 
+// index of record `rank` of step s in the tokenizer's record buffer: [steps][kRecInline] first, then [steps][the rest] from
+// word r2 on (TokSrc::rec / rec2)
+__device__ __forceinline__ int64_t rec_index(int64_t s, int rank, int64_t r2) {
+    return rank < kRecInline ? s * kRecInline + rank : r2 + s * (kRecPerStep - kRecInline) + (rank - kRecInline);
+}
 __device__ __forceinline__ uint32_t pack_rec(int pos, int len, int is_close, int cls, int exotic) {
     return (uint32_t)pos | ((uint32_t)len << 10) | ((len ? (uint32_t)is_close : 2u) << 17) | ((uint32_t)cls << 19) | ((uint32_t)exotic << 26);
 }
@@ -55,7 +60,7 @@ __device__ __forceinline__ uint32_t pack_rec(int pos, int len, int is_close, int
 // in text and frequent in adversarial text, and the byte-wise matcher costs ~10x the word compare, so it pays to run it
 // with all lanes busy instead of under the divergence of the pair it came from (cfg5: 8 of 32 lanes active before).
 __device__ __forceinline__ void tok_drain(const DevTags& tg, const uint8_t* __restrict__ bytes, int64_t total, uint32_t* __restrict__ rec,
-                                       const TokWarpScratch& W, int first, int n, int lane) {
+                                       int64_t r2, const TokWarpScratch& W, int first, int n, int lane) {
     if (lane < n) {
         const int64_t x = W.dpos[first + lane];
         const PtrAcc A{bytes};
@@ -64,7 +69,7 @@ __device__ __forceinline__ void tok_drain(const DevTags& tg, const uint8_t* __re
         int64_t ex;
         const int64_t tend = match_tag(tg, A, x, total, is_close != 0, cls, ex);
         const int len = tend >= 0 ? (int)(tend - x) : 0;
-        rec[(x >> 10) * kRecPerStep + W.drank[first + lane]] = pack_rec((int)(x & 1023), len, is_close, len ? cls : 0, len && ex >= 0);
+        rec[rec_index(x >> 10, W.drank[first + lane], r2)] = pack_rec((int)(x & 1023), len, is_close, len ? cls : 0, len && ex >= 0);
     }
 }
 
@@ -100,11 +105,11 @@ __device__ __forceinline__ bool tok_defer(TokWarpScratch& W, bool need, int64_t 
 //     deferred to the warp's list (tok_defer) and matched 32 at a time between pairs (tok_drain): cfg5 0.69 -> 0.50 ms.
 //     The sparse path does not defer: the extra ballot there cost cfg2's tokenizer 2.7 % for 5 % more on cfg5.
 // Returns true when something was deferred.
-// cnt / rec are indexed by absolute step (the caller may pass pointers shifted so that the steps of a tile land in shared
-// memory); steps >= nsteps are not written, bytes at and beyond `total` are never read.  A step with more than
+// cnt / rec are indexed by absolute step (rec through rec_index); steps >= nsteps are not written, bytes at and beyond
+// `total` are never read.  A step with more than
 // kRecPerStep candidates gets cnt = kRecOverflow and no records.
 __device__ __forceinline__ bool tokenize_pair(const DevTags& tg, const uint8_t* __restrict__ bytes, int64_t total, int64_t nsteps,
-                                              int64_t pr, int lane, uint8_t* cnt, uint32_t* rec, TokWarpScratch& W) {
+                                              int64_t pr, int lane, uint8_t* cnt, uint32_t* rec, int64_t r2, TokWarpScratch& W) {
     const int half = lane >> 4;
     const unsigned hm = half ? 0xFFFF0000u : 0x0000FFFFu;  // the lanes of this lane's step
     const int64_t a = (pr << 11) + lane * 64;
@@ -144,7 +149,7 @@ __device__ __forceinline__ bool tokenize_pair(const DevTags& tg, const uint8_t* 
             int is_close, cls, exotic;
             const int len = tag_at<false>(tg, bytes, total, a + b, is_close, cls, exotic);
             need = false;
-            if (!need) rec[step * kRecPerStep + rank] = pack_rec((lane & 15) * 64 + b, len, is_close, cls, exotic);
+            if (!need) rec[rec_index(step, rank, r2)] = pack_rec((lane & 15) * 64 + b, len, is_close, cls, exotic);
         }
         if ((lane & 15) == 0 && step < nsteps) cnt[step] = (uint8_t)tot;  // at most 16
         return false;
@@ -189,7 +194,7 @@ __device__ __forceinline__ bool tokenize_pair(const DevTags& tg, const uint8_t* 
                 const int len = tag_at<true>(tg, bytes, total, x, is_close, cls, exotic);
                 rank = i - (sl ? first1 : 0);
                 need = len < 0;
-                if (!need) rec[st * kRecPerStep + rank] = pack_rec(pos & 1023, len, is_close, cls, exotic);
+                if (!need) rec[rec_index(st, rank, r2)] = pack_rec(pos & 1023, len, is_close, cls, exotic);
             }
         }
         deferred |= tok_defer(W, need, x, rank, lane);
@@ -215,6 +220,7 @@ __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant_
     int64_t nsteps = (total + 1023) >> 10;
     if (nsteps > max_steps) nsteps = max_steps;
     const int64_t npairs = (nsteps + 1) >> 1;
+    const int64_t r2 = max_steps * kRecInline;  // where the second record array starts (words)
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
     TokWarpScratch& W = s_tok[threadIdx.x >> 5];
     if (lane == 0) W.ndef = 0;
@@ -224,19 +230,19 @@ __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant_
             const int64_t an = ((pr + nwarps) << 11) + lane * 128;
             if (lane < 16 && an + 128 <= total) asm volatile("prefetch.global.L2 [%0];" ::"l"(bytes + an));
         }
-        if (!tokenize_pair(tg, bytes, total, nsteps, pr, lane, cnt, rec, W)) continue;
+        if (!tokenize_pair(tg, bytes, total, nsteps, pr, lane, cnt, rec, r2, W)) continue;
         int nd = W.ndef;
         if (nd >= 32) {  // full warps' worth of deferred candidates
             do {
                 nd -= 32;
-                tok_drain(tg, bytes, total, rec, W, nd, 32, lane);
+                tok_drain(tg, bytes, total, rec, r2, W, nd, 32, lane);
             } while (nd >= 32);
             __syncwarp();
             if (lane == 0) W.ndef = nd;
             __syncwarp();
         }
     }
-    if (W.ndef) tok_drain(tg, bytes, total, rec, W, 0, W.ndef, lane);
+    if (W.ndef) tok_drain(tg, bytes, total, rec, r2, W, 0, W.ndef, lane);
 }
 
 }  // namespace qb

@@ -11,8 +11,10 @@ namespace qb {
 
 // Token records written by the tokenizer pass (qb_tok.cuh), one group per absolute 1 KiB step of the flat buffer:
 //   cnt[step]  number of records (0..kRecPerStep), kRecOverflow when the step had more '<' than fit
-//   rec[step * kRecPerStep + k], in position order (a walker keeps the first kRecInline of a step in registers and
-//   fetches the rest, lane per record, only for the rare step that has more):
+//   record k of a step, in position order: the first kRecInline of every step sit side by side in `rec` (32 bytes per
+//   step: a walker reads one sector per step, four steps per line - with all 48 slots of a step in one place every
+//   step cost a 128-byte line of DRAM traffic for its one or two records), the rest in `rec2` (a walker keeps the
+//   first kRecInline of a step in registers and fetches the rest, lane per record, only for the rare step that has more):
 //     bits 0-9 position inside the step | 10-16 tag length in bytes (0 for a literal '<') | 17-18 kind
 //     (0 open tag, 1 close tag, 2 '<' that starts no complete tag) | 19-25 backreference class | 26 the tag uses a
 //     U+0130/U+0131/U+017F spelling (the walker re-reads the bytes when that matters)
@@ -21,11 +23,16 @@ constexpr int kRecInline = 8;
 constexpr int kRecOverflow = 255;
 struct TokSrc {
     const uint8_t* cnt = nullptr;
-    const uint32_t* rec = nullptr;
+    const uint32_t* rec = nullptr;   // [step][kRecInline]
+    const uint32_t* rec2 = nullptr;  // [step][kRecPerStep - kRecInline]
     int64_t nsteps = 0;  // steps the record arrays were sized for (from the caller's byte bound, out_capacity)
     // Record count of step s.  A step beyond the arrays reads as "overflowed": when a caller states a byte bound below the
     // real input size the units out there are walked from their bytes instead of from records that were never written.
     __device__ __forceinline__ int count(int64_t s) const { return s < nsteps ? (int)cnt[s] : kRecOverflow; }
+    __device__ __forceinline__ const uint32_t* head(int64_t s) const { return rec + s * kRecInline; }  // records 0..kRecInline-1
+    // p[k] is record k of step s for k >= kRecInline
+    __device__ __forceinline__ const uint32_t* tail(int64_t s) const { return rec2 + s * (kRecPerStep - kRecInline) - kRecInline; }
+    __device__ __forceinline__ uint32_t get(int64_t s, int k) const { return k < kRecInline ? head(s)[k] : tail(s)[k]; }
 };
 __device__ __forceinline__ uint32_t rec_select(const uint4& a, const uint4& b, int k) {
     switch (k) {
@@ -736,7 +743,7 @@ struct StreamRunWalker {
                         cnt = ts.count(sj);
                         if (cnt == kRecOverflow) cnt = -1;
                         if (cnt > 0) {
-                            const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);
+                            const uint4* rp = reinterpret_cast<const uint4*>(ts.head(sj));
                             ra = rp[0];
                             if (cnt > 4) rb = rp[1];
                         }
@@ -777,7 +784,7 @@ struct StreamRunWalker {
                             }
                         } else {  // a dense step: one record per lane straight from memory, 32 at a time
                             for (int k0 = 0; k0 < c; k0 += 32) {
-                                const uint32_t rd = k0 + lane < c ? ts.rec[(S0 + j) * kRecPerStep + k0 + lane] : 0u;
+                                const uint32_t rd = k0 + lane < c ? ts.get(S0 + j, k0 + lane) : 0u;
                                 for (int k = 0; k < 32 && k0 + k < c; k++) handle(__shfl_sync(kFull, rd, k));
                             }
                         }
@@ -921,7 +928,7 @@ struct StripRunWalker {
                         cnt = ts.count(sj);
                         if (cnt == kRecOverflow) cnt = -1;
                         if (cnt > 0) {
-                            const uint4* rp = reinterpret_cast<const uint4*>(ts.rec + sj * kRecPerStep);
+                            const uint4* rp = reinterpret_cast<const uint4*>(ts.head(sj));
                             ra = rp[0];
                             if (cnt > 4) rb = rp[1];
                         }
@@ -934,7 +941,7 @@ struct StripRunWalker {
                 const int sb0 = (int)((S0 << 10) - ustart);
                 if (pass == 0) {  // pass A: last closer per class, every lane over its own step
                     for (int k = 0; k < cnt; k++) {
-                        const uint32_t r = k < kRecInline ? rec_select(ra, rb, k) : ts.rec[sj * kRecPerStep + k];
+                        const uint32_t r = k < kRecInline ? rec_select(ra, rb, k) : ts.tail(sj)[k];
                         if (((r >> 17) & 3) != 1) continue;
                         const int x = sb0 + lane * 1024 + (int)(r & 1023);
                         const int tend = x + (int)((r >> 10) & 127);
@@ -980,7 +987,7 @@ struct StripRunWalker {
                             // Every lane decodes its own record and looks up liveness; the automaton then only visits the
                             // records that change its state (ballot + find-first-set), not every record.
                             for (int k0 = 0; k0 < c && !dead; k0 += 32) {
-                                const uint32_t r = k0 + lane < c ? ts.rec[(S0 + j) * kRecPerStep + k0 + lane] : (2u << 17);
+                                const uint32_t r = k0 + lane < c ? ts.get(S0 + j, k0 + lane) : (2u << 17);
                                 const int kind = (r >> 17) & 3;
                                 const int x = sb0 + j * 1024 + (int)(r & 1023);
                                 const int tend = x + (int)((r >> 10) & 127);

@@ -186,7 +186,7 @@ __device__ __forceinline__ void prefetch_unit_meta(const TokSrc& ts, const uint8
     else if (lane == 1) p = ts.cnt + s1;
     else if (lane == 2) p = bytes + a;
     else if (lane == 3) p = bytes + b - 1;
-    else if (s0 + (lane - 4) <= s1) p = ts.rec + (s0 + (lane - 4)) * kRecPerStep;  // one step's records per 128-byte line
+    else if (s0 + (lane - 4) <= s1) p = ts.head(s0 + (lane - 4));  // the first records of four steps per 128-byte line
     if (p) asm volatile("prefetch.L1 [%0];" ::"l"(p));
 }
 
@@ -524,6 +524,12 @@ __device__ __forceinline__ void gather_pooled(const int2* __restrict__ runs, int
         int2 run = make_int2(0, 0);
         if (i < nruns) run = runs[i];
         const int len = run.y - run.x;
+        if (len > 0) {  // the first lines of every run of the batch on their way to L2 before the first copy waits on one
+            const uint8_t* a = src + run.x;  // (cfg5's copy 0.48 -> 0.44 ms)
+            const uint8_t* base = reinterpret_cast<const uint8_t*>(reinterpret_cast<uintptr_t>(a) & ~(uintptr_t)127);
+            const int bytes = min((int)(a - base) + len, 8 * 128);
+            for (int o = 0; o < bytes; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(base + o));
+        }
         int incl = len;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -556,7 +562,10 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
     const int64_t total = in_off[n_resp];
     for (int64_t r = (int64_t)blockIdx.x * kWarpsPerBlock + wib; r < n_resp; r += (int64_t)gridDim.x * kWarpsPerBlock) {
         // (prefetching the next response's metadata lines here made the kernel slower: cfg3 1.12 -> 1.17 ms; so did loading
-        // all of a unit's metadata - offsets, destination, length, descriptor, runs - side by side up front: 1.38 ms)
+        // all of a unit's metadata - offsets, destination, length, descriptor, runs - side by side up front: 1.38 ms; so
+        // did a software pipeline that loads the NEXT response's metadata into registers before this one is copied:
+        // 1.09 -> 1.31 ms at 48 registers, 1.17 at 64; and taking the long responses first by ticket (a queue filled by
+        // the count kernels): cfg5 -3 %, cfg3 +3.5 %)
         const int64_t a = in_off[r], b = in_off[r + 1];
         const int64_t de = dst[r];
         if (de < 0) {  // excluded from the join
@@ -984,7 +993,7 @@ static int env_int(const char* name, int dflt) {
 static int64_t steps_for(int64_t byte_bound) { return (byte_bound < 0 ? 0 : byte_bound) / 1024 + 2; }
 static size_t tok_scratch_bytes(int64_t byte_bound) {
     const int64_t st = steps_for(byte_bound);
-    return align256((size_t)st) + align256((size_t)st * kRecPerStep * 4) + 256;
+    return align256((size_t)st) + align256((size_t)st * kRecPerStep * 4) + 256;  // cnt | rec [st][kRecInline] | rec2 [st][the rest]
 }
 
 // tokenizer pass over the flat buffer; returns where the records are
@@ -1003,6 +1012,7 @@ static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const in
     LAUNCHED("tokenize_kernel");
     ts.cnt = cnt;
     ts.rec = rec;
+    ts.rec2 = rec + st * kRecInline;
     ts.nsteps = st;
     return ts;
 }

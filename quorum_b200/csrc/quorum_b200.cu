@@ -197,6 +197,9 @@ __device__ __forceinline__ void prefetch_unit_meta(const TokSrc& ts, const uint8
 // more classes than a lane tracks, pool exhausted, an overflowed step) need a whole warp each; they go to a queue that
 // strip_count_long_kernel drains with every warp of the GPU, one response per warp - walked where they are found, 32 long
 // responses would run one after the other on ONE warp (a batch of 4,096 responses of 256 KiB ran on 128 warps: 1.5 ms).
+// (Tried: the long responses walked inside strip_count_kernel by its first 148..444 blocks - a contiguous share of the
+// responses per block, its warps taking the long ones by ticket - so that the two kinds of walk overlap: cfg5's count
+// 0.34 + 0.20 -> 0.61..0.75 ms, the static shares are uneven and fewer warps are left for the long walks.)
 struct LongQueue {
     int64_t* items = nullptr;          // response indices (the `dst` array, not needed before the request offsets)
     unsigned long long* count = nullptr;

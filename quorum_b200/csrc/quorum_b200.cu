@@ -1346,14 +1346,17 @@ int qb200_sse_frame_batch(const uint8_t* in_bytes, const int64_t* in_off, int64_
     }
     int64_t* lens = (int64_t*)scratch;
     int64_t* partial = (int64_t*)((uint8_t*)scratch + align256((size_t)(n_items + 2) * 8));
-    int64_t blocks = (n_items + 7) / 8;
+    const int64_t groups = (n_items + 31) / 32;  // a warp takes 32 consecutive items
+    int64_t blocks = (groups + 7) / 8;
     if (blocks > 148 * 32) blocks = 148 * 32;
     sse_count_kernel<<<(unsigned)blocks, 256, 0, stream>>>(in_bytes, in_off, n_items, item_prefix, prefix_off, suffix_len, flags,
                                                           lens);
     LAUNCHED("sse_count_kernel");
     launch_scan(lens, n_items, out_off, partial, stream);
-    sse_write_kernel<<<(unsigned)blocks, 256, 0, stream>>>(in_bytes, in_off, n_items, item_prefix, prefix_bytes, prefix_off, suffix,
-                                                          suffix_len, out_off, out_bytes);
+    int64_t wblocks = (groups + kSseWarps - 1) / kSseWarps;
+    if (wblocks > 148 * 32) wblocks = 148 * 32;
+    sse_write_kernel<<<(unsigned)wblocks, kSseWarps * 32, 0, stream>>>(in_bytes, in_off, n_items, item_prefix, prefix_bytes, prefix_off,
+                                                                      n_prefix, suffix, suffix_len, out_off, out_bytes);
     LAUNCHED("sse_write_kernel");
     CUDA_TRY(cudaGetLastError());
     return QB200_OK;

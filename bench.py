@@ -616,6 +616,9 @@ def measure(ctx, W, args, want_e2e=True, want_kernels=True, sustained_s=1.0):
         roofline["kernels_source"] = ("qb200_profile_begin/end: CUDA events after each launch on the launching stream, separate pass "
                                       "after the timed region")
     tj = ctx.traffic.get(W.name)
+    # the ncu capture is of the workload at its configs size: a batch of another size (the sharded 10 GB cfg5) has none
+    if tj and tj.get("dram_bytes_per_launch") and not 0.5 < tj["dram_bytes_per_launch"] / alg_bytes < 4.0:
+        tj = None
     if tj:
         roofline["traffic"] = tj.get("dram_bytes_per_launch")
         roofline["traffic_ratio"] = (tj.get("dram_bytes_per_launch") or 0) / alg_bytes if tj.get("dram_bytes_per_launch") else None

@@ -199,7 +199,10 @@ __device__ __forceinline__ void prefetch_unit_meta(const TokSrc& ts, const uint8
 // responses would run one after the other on ONE warp (a batch of 4,096 responses of 256 KiB ran on 128 warps: 1.5 ms).
 // (Tried: the long responses walked inside strip_count_kernel by its first 148..444 blocks - a contiguous share of the
 // responses per block, its warps taking the long ones by ticket - so that the two kinds of walk overlap: cfg5's count
-// 0.34 + 0.20 -> 0.61..0.75 ms, the static shares are uneven and fewer warps are left for the long walks.)
+// 0.34 + 0.20 -> 0.61..0.75 ms, the static shares are uneven and fewer warps are left for the long walks.  And: the long
+// responses listed by size and strip_count_long_kernel run on a second stream beside strip_count_kernel: cfg5 1.492 ->
+// 1.501 ms - the two kernels use 50 % and 40 % of the issue slots at 2.4 and 13 active lanes per instruction, so side by
+// side they take as long as one after the other; fewer instructions, not more overlap, is what the count phase needs.)
 struct LongQueue {
     int64_t* items = nullptr;          // response indices (the `dst` array, not needed before the request offsets)
     unsigned long long* count = nullptr;

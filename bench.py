@@ -615,6 +615,18 @@ def measure(ctx, W, args, want_e2e=True, want_kernels=True, sustained_s=1.0):
         roofline["kernels"] = kernels
         roofline["kernels_source"] = ("qb200_profile_begin/end: CUDA events after each launch on the launching stream, separate pass "
                                       "after the timed region")
+        # the two kernels that touch the text, each against its OWN algorithmic bytes: the tokenizer reads every input byte
+        # once (+ one count byte per KiB written); the copy kernel reads every kept byte and writes it once (+ 16 B of
+        # offsets per item).  The whole-call fraction above is lower because the kept bytes are read by both.
+        own = {"tokenize_kernel": W.total_in + W.total_in // 1024,
+               "strip_copy_kernel": 2 * total_out + 16 * W.n_items, "stream_finish_kernel": 2 * total_out + 16 * W.n_units}
+        per = []
+        for k in kernels:
+            if k["name"] in own and k["ms_per_step"] > 0:
+                a = own[k["name"]] / (k["ms_per_step"] * 1e-3) / 1e9
+                per.append({"name": k["name"], "algorithmic_bytes_per_launch": int(own[k["name"]]), "achieved": a, "frac": a / ctx.peak})
+        if per:
+            roofline["dominant_kernels"] = per
     tj = ctx.traffic.get(W.name)
     # the ncu capture is of the workload at its configs size: a batch of another size (the sharded 10 GB cfg5) has none
     if tj and tj.get("dram_bytes_per_launch") and not 0.5 < tj["dram_bytes_per_launch"] / alg_bytes < 4.0:

@@ -480,17 +480,10 @@ request_offsets_kernel(const int64_t* __restrict__ in_off, const int64_t* __rest
 
 // Warp-cooperative copy of a unit's kept runs (descriptor) to dst: run i goes to dst + held_kept + (lengths before it).
 // PHASE 0: prefetch the source lines and copy; 1: prefetch only; 2: copy only (the caller put work between the two).
+// gather_runs: the runs are in registers (lane i < nruns holds run i as [rs, re) relative to src).
 template <int PHASE>
-__device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, const uint8_t* src, uint8_t* dst,
+__device__ __forceinline__ void gather_runs(int nruns, int rs, int re, int held_kept, const uint8_t* src, uint8_t* dst,
                                             const uint8_t* src_hi, int lane) {
-    const int nruns = dp->nruns;
-    if (nruns <= 0) return;
-    int rs = 0, re = 0;
-    if (lane < kDescRuns && lane < nruns) {
-        rs = dp->run_s[lane];
-        re = dp->run_e[lane];
-        if ((dp->flags & 2) && lane == nruns - 1 && dp->rlast < re) re = dp->rlast > rs ? dp->rlast : rs;  // open-ended final run
-    }
     const int len = re - rs;
     int incl = len;
 #pragma unroll
@@ -498,7 +491,7 @@ __device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, con
         int t = __shfl_up_sync(kFull, incl, d);
         if (lane >= d) incl += t;
     }
-    const int off = dp->held_kept + incl - len;
+    const int off = held_kept + incl - len;
     const bool tiny = __shfl_sync(kFull, incl, kDescRuns - 1) <= 64 * nruns;  // short runs: one run per lane, byte by byte
     if (PHASE != 2 && !tiny) {
         for (int i = 0; i < nruns; i++) {  // get every source line of every run moving before the first copy waits on one
@@ -518,6 +511,20 @@ __device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, con
         const int s_i = __shfl_sync(kFull, rs, i), l_i = __shfl_sync(kFull, len, i), o_i = __shfl_sync(kFull, off, i);
         if (l_i > 0) warp_copy_fast(dst + o_i, src + s_i, l_i, src_hi, lane);
     }
+}
+
+template <int PHASE>
+__device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, const uint8_t* src, uint8_t* dst,
+                                            const uint8_t* src_hi, int lane) {
+    const int nruns = dp->nruns;
+    if (nruns <= 0) return;
+    int rs = 0, re = 0;
+    if (lane < kDescRuns && lane < nruns) {
+        rs = dp->run_s[lane];
+        re = dp->run_e[lane];
+        if ((dp->flags & 2) && lane == nruns - 1 && dp->rlast < re) re = dp->rlast > rs ? dp->rlast : rs;  // open-ended final run
+    }
+    gather_runs<PHASE>(nruns, rs, re, dp->held_kept, src, dst, src_hi, lane);
 }
 
 // The same for a unit whose runs live in the pool (more than kDescRuns): 32 runs at a time, one per lane for the offsets,
@@ -574,6 +581,18 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
         // the count kernels): cfg5 -3 %, cfg3 +3.5 %)
         const int64_t a = in_off[r], b = in_off[r + 1];
         const int64_t de = dst[r];
+        // the descriptor's first 32 bytes (run count, kept length, flags) and its runs fetched beside the offsets, not
+        // after them: the kept length then needs no load of klen[r] behind the `de` test, the run count none behind that
+        // and the runs none behind the run count - one round trip for a response's metadata instead of four (cfg3
+        // 2.006 -> 1.940 ms; the same loads for the NEXT response, or prefetches of its lines, made it slower each time)
+        int4 h0 = make_int4(-1, 0, 0, 0), h1 = make_int4(0, 0, 0, 0);
+        int rs0 = 0, re0 = 0;
+        if (hide && desc) {
+            h0 = reinterpret_cast<const int4*>(desc + r)[0];  // nruns, total, held_kept, depth
+            h1 = reinterpret_cast<const int4*>(desc + r)[1];  // last_tok_end, rlast, flags, held_len
+            rs0 = desc[r].run_s[lane & (kDescRuns - 1)];       // and its runs, one per lane (pooled: the pool index)
+            re0 = desc[r].run_e[lane & (kDescRuns - 1)];
+        }
         if (de < 0) {  // excluded from the join
             if (resp_out_len && lane == 0) resp_out_len[r] = 0;
             continue;
@@ -581,17 +600,25 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
         const int64_t d = de >> 1;
         if (de & 1)  // the separator between this response and the previous included one of its request
             for (int i = lane; i < sep_len; i += 32) out[d - sep_len + i] = sep[i];
-        const int64_t kl = hide ? klen[r] : (b - a);
+        const int nr = h0.x;
+        const int64_t kl = !hide ? (b - a) : nr > 0 ? (int64_t)h0.y : klen[r];
         if (resp_out_len && lane == 0) resp_out_len[r] = kl;
         if (!hide) {
             warp_copy<true>(out + d, in + a, b - a, in + total, lane);
         } else if (kl > 0) {
-            const int nr = desc ? desc[r].nruns : -1;
-            if (nr >= 0 && (desc[r].flags & kDescPooled)) {
-                const unsigned long long at = (unsigned long long)(uint32_t)desc[r].run_s[0] | ((unsigned long long)(uint32_t)desc[r].run_s[1] << 32);
+            if (nr >= 0 && ((uint32_t)h1.z & kDescPooled)) {
+                const unsigned long long at = (unsigned long long)(uint32_t)__shfl_sync(kFull, rs0, 0) |
+                                              ((unsigned long long)(uint32_t)__shfl_sync(kFull, rs0, 1) << 32);
                 gather_pooled(pool.runs + at, nr, in + a, out + d, in + total, lane);
-            } else if (nr >= 0) {
-                gather_unit<0>(desc + r, in + a, out + d, in + total, lane);
+            } else if (nr > 0) {
+                int rs = 0, re = 0;
+                if (lane < kDescRuns && lane < nr) {
+                    rs = rs0;
+                    re = re0;
+                    if ((h1.z & 2) && lane == nr - 1 && h1.y < re) re = h1.y > rs ? h1.y : rs;  // open-ended final run
+                }
+                gather_runs<0>(nr, rs, re, h0.z, in + a, out + d, in + total, lane);
+            } else if (nr == 0) {
             } else if (nr == -2) {  // 9..32 kept runs: walk the records again and copy from the lanes
                 strip_copy_wide(tg, in, total, a, b - a, lastclose[wib], lane, ts, kl, out + d);
             } else {

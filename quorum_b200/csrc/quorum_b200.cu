@@ -513,20 +513,6 @@ __device__ __forceinline__ void gather_runs(int nruns, int rs, int re, int held_
     }
 }
 
-template <int PHASE>
-__device__ __forceinline__ void gather_unit(const UnitDesc* __restrict__ dp, const uint8_t* src, uint8_t* dst,
-                                            const uint8_t* src_hi, int lane) {
-    const int nruns = dp->nruns;
-    if (nruns <= 0) return;
-    int rs = 0, re = 0;
-    if (lane < kDescRuns && lane < nruns) {
-        rs = dp->run_s[lane];
-        re = dp->run_e[lane];
-        if ((dp->flags & 2) && lane == nruns - 1 && dp->rlast < re) re = dp->rlast > rs ? dp->rlast : rs;  // open-ended final run
-    }
-    gather_runs<PHASE>(nruns, rs, re, dp->held_kept, src, dst, src_hi, lane);
-}
-
 // The same for a unit whose runs live in the pool (more than kDescRuns): 32 runs at a time, one per lane for the offsets,
 // then run by run - long runs by the whole warp with 16-byte stores, short ones as lane-strided bytes (coalesced).
 __device__ __forceinline__ void gather_pooled(const int2* __restrict__ runs, int nruns, const uint8_t* src, uint8_t* dst,
@@ -578,7 +564,8 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
         // all of a unit's metadata - offsets, destination, length, descriptor, runs - side by side up front: 1.38 ms; so
         // did a software pipeline that loads the NEXT response's metadata into registers before this one is copied:
         // 1.09 -> 1.31 ms at 48 registers, 1.17 at 64; and taking the long responses first by ticket (a queue filled by
-        // the count kernels): cfg5 -3 %, cfg3 +3.5 %)
+        // the count kernels): cfg5 -3 %, cfg3 +3.5 %; blocks of 4 or 2 warps instead of 8, so that a block's slot is not
+        // held by one long response: cfg5 -1.7 / -2 %, cfg3 -0.3 %, cfg4 +0.6 / +0.8 %)
         const int64_t a = in_off[r], b = in_off[r + 1];
         const int64_t de = dst[r];
         // the descriptor's first 32 bytes (run count, kept length, flags) and its runs fetched beside the offsets, not
@@ -857,7 +844,12 @@ stream_finish_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restri
     const int64_t total = chunk_off[n_chunks];
     for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
         const StreamDesc* d = desc + s;
-        const int nruns = d->nruns;
+        // everything the copy needs from the descriptor in one round trip (see strip_copy_kernel)
+        const int4 h0 = reinterpret_cast<const int4*>(d)[0];  // nruns, total, held_kept, depth
+        const int4 h1 = reinterpret_cast<const int4*>(d)[1];  // last_tok_end, rlast, flags, held_len
+        const int rs0 = d->run_s[lane & (kDescRuns - 1)], re0 = d->run_e[lane & (kDescRuns - 1)];
+        const int64_t ustart = d->ustart;
+        const int nruns = h0.x;
         const int64_t base = bases[s];
         if (nruns < 0) {
             const int64_t c0 = stream_off[s], c1 = stream_off[s + 1];
@@ -866,9 +858,17 @@ stream_finish_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restri
             stream_copy_slow(tg, bytes, total, chunk_off + c0, c1 - c0, lane, flags, st_in ? &si : nullptr,
                              st_out ? st_out + s : nullptr, base, out, out_chunk_off, c0);
         } else {
-            const int hk = d->held_kept;
+            const int hk = h0.z;
             if (lane < hk) out[base + lane] = d->held[lane];
-            if (nruns > 0) gather_unit<0>(d, bytes + d->ustart, out + base, bytes + total, lane);
+            if (nruns > 0) {
+                int rs = 0, re = 0;
+                if (lane < kDescRuns && lane < nruns) {
+                    rs = rs0;
+                    re = re0;
+                    if ((h1.z & 2) && lane == nruns - 1 && h1.y < re) re = h1.y > rs ? h1.y : rs;  // open-ended final run
+                }
+                gather_runs<0>(nruns, rs, re, hk, bytes + ustart, out + base, bytes + total, lane);
+            }
         }
         __syncwarp();
     }

@@ -203,6 +203,9 @@ __device__ __forceinline__ void prefetch_unit_meta(const TokSrc& ts, const uint8
 // responses listed by size and strip_count_long_kernel run on a second stream beside strip_count_kernel: cfg5 1.492 ->
 // 1.501 ms - the two kernels use 50 % and 40 % of the issue slots at 2.4 and 13 active lanes per instruction, so side by
 // side they take as long as one after the other; fewer instructions, not more overlap, is what the count phase needs.)
+// (Tried: the record counts and first records of a warp's 32 consecutive responses fetched into shared memory with
+// coalesced 16-byte loads, the lanes walking from there: cfg3's count 0.188 -> 0.234 ms at three blocks per SM; the
+// generic-address loads and the lost block cost more than the sector-per-lane loads they replace.)
 struct LongQueue {
     int64_t* items = nullptr;          // response indices (the `dst` array, not needed before the request offsets)
     unsigned long long* count = nullptr;

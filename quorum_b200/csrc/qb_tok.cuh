@@ -56,20 +56,17 @@ __device__ __forceinline__ uint32_t pack_rec(int pos, int len, int is_close, int
     return (uint32_t)pos | ((uint32_t)len << 10) | ((len ? (uint32_t)is_close : 2u) << 17) | ((uint32_t)cls << 19) | ((uint32_t)exotic << 26);
 }
 
-// The exact matcher for deferred candidates [first, first + n) of the warp's list, one per lane: fold spellings are rare
-// in text and frequent in adversarial text, and the byte-wise matcher costs ~10x the word compare, so it pays to run it
-// with all lanes busy instead of under the divergence of the pair it came from (cfg5: 8 of 32 lanes active before).
+// The tag test for deferred candidates [first, first + n) of the warp's list, one per lane.  Matching a candidate where
+// it is found runs ~80 instructions (the byte-wise matcher for fold spellings ~10x that) with only the lanes that hold
+// one active - two or three of 32 in ordinary text - and that was half of the tokenizer's issue slots; collected
+// across pairs and matched 32 at a time the same work is a few instructions per candidate.
 __device__ __forceinline__ void tok_drain(const DevTags& tg, const uint8_t* __restrict__ bytes, int64_t total, uint32_t* __restrict__ rec,
                                        int64_t r2, const TokWarpScratch& W, int first, int n, int lane) {
     if (lane < n) {
         const int64_t x = W.dpos[first + lane];
-        const PtrAcc A{bytes};
-        const int is_close = bytes[x + 1] == '/';
-        int cls = 0;
-        int64_t ex;
-        const int64_t tend = match_tag(tg, A, x, total, is_close != 0, cls, ex);
-        const int len = tend >= 0 ? (int)(tend - x) : 0;
-        rec[rec_index(x >> 10, W.drank[first + lane], r2)] = pack_rec((int)(x & 1023), len, is_close, len ? cls : 0, len && ex >= 0);
+        int is_close, cls, exotic;
+        const int len = tag_at<false>(tg, bytes, total, x, is_close, cls, exotic);
+        rec[rec_index(x >> 10, W.drank[first + lane], r2)] = pack_rec((int)(x & 1023), len, is_close, cls, exotic);
     }
 }
 
@@ -103,7 +100,9 @@ __device__ __forceinline__ bool tok_defer(TokWarpScratch& W, bool need, int64_t 
 //     0.65 ms); a candidate's record goes straight to its slot: its rank inside its step is its list index minus the
 //     step's first index.  Candidates whose window holds a fold-form lead byte need the exact byte-wise matcher: they are
 //     deferred to the warp's list (tok_defer) and matched 32 at a time between pairs (tok_drain): cfg5 0.69 -> 0.50 ms.
-//     The sparse path does not defer: the extra ballot there cost cfg2's tokenizer 2.7 % for 5 % more on cfg5.
+//   The sparse path defers EVERY candidate (position and rank are known, the record slot waits): cfg3's tokenizer
+//     0.74 -> 0.69 ms (6.0 TB/s), cfg2 0.201 -> 0.192, cfg4 0.70 -> 0.68, cfg5 0.52 -> 0.48.  (Deferring only the
+//     candidates that need the exact matcher there cost more in ballots than it saved.)
 // Returns true when something was deferred.
 // cnt / rec are indexed by absolute step (rec through rec_index); steps >= nsteps are not written, bytes at and beyond
 // `total` are never read.  A step with more than
@@ -146,13 +145,10 @@ __device__ __forceinline__ bool tokenize_pair(const DevTags& tg, const uint8_t* 
         const int rank = __popc(any & hm & (0xffffffffu >> (31 - lane))) - 1;
         if (nr && step < nsteps) {
             b = lt0 ? __ffs(lt0) - 1 : 32 + __ffs(lt1) - 1;
-            int is_close, cls, exotic;
-            const int len = tag_at<false>(tg, bytes, total, a + b, is_close, cls, exotic);
-            need = false;
-            if (!need) rec[rec_index(step, rank, r2)] = pack_rec((lane & 15) * 64 + b, len, is_close, cls, exotic);
+            need = true;
         }
         if ((lane & 15) == 0 && step < nsteps) cnt[step] = (uint8_t)tot;  // at most 16
-        return false;
+        return tok_defer(W, need, a + b, rank, lane);
     }
     // dense: ranks from a warp scan, candidates compacted into the list, one per lane per round
     int incl = nr;

@@ -774,6 +774,7 @@ stream_offsets_kernel(const int64_t* __restrict__ chunk_off, const int64_t* __re
         // which stream owns each boundary: start from the owner of the tile's first boundary (written by the count
         // kernel) and step over the stream ends in between (a tile usually lies inside one or two streams)
         int sc = sid[(i0 - lane) / (32 * PER)];
+        int64_t send = stream_off[sc + 1];  // first chunk of the next stream (kept in a register: one load per stream crossed)
 #pragma unroll
         for (int j = 0; j < PER; j++) {
             const int64_t i = i0 + 32 * j;
@@ -781,8 +782,9 @@ stream_offsets_kernel(const int64_t* __restrict__ chunk_off, const int64_t* __re
             if (i < nb) {
                 const int64_t k = cb + i;  // chunk index
                 int steps = 0;
-                while (k >= stream_off[sc + 1]) {
+                while (k >= send) {
                     sc++;
+                    send = stream_off[sc + 1];
                     if (++steps == 16) {  // many short or empty streams: binary search for the last stream starting at or before k
                         int64_t lo = sc, hi = n_streams - 1;
                         while (lo < hi) {
@@ -791,6 +793,7 @@ stream_offsets_kernel(const int64_t* __restrict__ chunk_off, const int64_t* __re
                             else hi = mid - 1;
                         }
                         sc = (int)lo;
+                        send = stream_off[sc + 1];
                         break;
                     }
                 }

@@ -37,14 +37,16 @@ __device__ __forceinline__ int tag_at(const DevTags& tg, const uint8_t* buf, int
 
 __device__ __forceinline__ uint32_t lt_any16(const uint4& v) { return lt_any(v.x) | lt_any(v.y) | lt_any(v.z) | lt_any(v.w); }
 
-// Per-warp scratch of the tokenizer (shared memory): the candidate list of a dense pair.
-constexpr int kTokList = 2 * kRecPerStep;
-constexpr int kTokDefer = 32 + 2 * kRecPerStep;
+// Per-warp scratch of the tokenizer (shared memory): candidates waiting for their tag test.  Two lists in one array:
+// fresh candidates grow from index 0 up (every '<' found, position + rank inside its step), candidates that turned out to
+// need the exact byte-wise matcher grow from the last index down.  Between pairs at most 31 of each wait; a pair adds at
+// most 2 * kRecPerStep fresh ones.
+constexpr int kTokDefer = 64 + 2 * kRecPerStep;
 struct __align__(8) TokWarpScratch {
-    int64_t dpos[kTokDefer];   // deferred candidates (need the exact byte matcher): absolute position ...
+    int64_t dpos[kTokDefer];   // absolute position of the '<' ...
     uint8_t drank[kTokDefer];  // ... and rank inside its step (= record slot)
-    int ndef;                  // entries waiting in dpos / drank
-    uint16_t list[kTokList];   // positions (inside the 2 KiB pair) of the '<' candidates, in position order
+    int ndef;                  // fresh entries: [0, ndef)
+    int nex;                   // entries for the exact matcher: [kTokDefer - nex, kTokDefer)
 };
 
 // index of record `rank` of step s in the tokenizer's record buffer: [steps][kRecInline] first, then [steps][the rest] from
@@ -56,23 +58,51 @@ __device__ __forceinline__ uint32_t pack_rec(int pos, int len, int is_close, int
     return (uint32_t)pos | ((uint32_t)len << 10) | ((len ? (uint32_t)is_close : 2u) << 17) | ((uint32_t)cls << 19) | ((uint32_t)exotic << 26);
 }
 
-// The tag test for deferred candidates [first, first + n) of the warp's list, one per lane.  Matching a candidate where
-// it is found runs ~80 instructions (the byte-wise matcher for fold spellings ~10x that) with only the lanes that hold
-// one active - two or three of 32 in ordinary text - and that was half of the tokenizer's issue slots; collected
-// across pairs and matched 32 at a time the same work is a few instructions per candidate.
-__device__ __forceinline__ void tok_drain(const DevTags& tg, const uint8_t* __restrict__ bytes, int64_t total, uint32_t* __restrict__ rec,
-                                       int64_t r2, const TokWarpScratch& W, int first, int n, int lane) {
+// The tag test for deferred candidates, one per lane.  Matching a candidate where it is found runs ~80 instructions (the
+// byte-wise matcher for fold spellings ~10x that) with only the lanes that hold one active - two or three of 32 in
+// ordinary text - and that was half of the tokenizer's issue slots; collected across pairs and matched 32 at a time the
+// same work is a few instructions per candidate.  Two stages, each with all lanes on the same code: the word-compare
+// matcher for fresh candidates [first, first + n); those whose window holds a fold-form lead byte move to the second list
+// (returns how many), which tok_drain_exact works off with the byte-wise matcher.
+__device__ __forceinline__ int tok_drain_fast(const DevTags& tg, const uint8_t* __restrict__ bytes, int64_t total, uint32_t* __restrict__ rec,
+                                              int64_t r2, TokWarpScratch& W, int first, int n, int nex, int lane) {
+    bool need = false;
+    int64_t x = 0;
+    int rank = 0;
+    if (lane < n) {
+        x = W.dpos[first + lane];
+        rank = W.drank[first + lane];
+        int is_close, cls, exotic;
+        const int len = tag_at<true>(tg, bytes, total, x, is_close, cls, exotic);
+        need = len < 0;
+        if (!need) rec[rec_index(x >> 10, rank, r2)] = pack_rec((int)(x & 1023), len, is_close, cls, exotic);
+    }
+    const unsigned m = __ballot_sync(kFull, need);  // (every lane has read its entry: the slots may be reused now)
+    if (need) {
+        const int k = kTokDefer - 1 - (nex + __popc(m & ((1u << lane) - 1u)));
+        W.dpos[k] = x;
+        W.drank[k] = (uint8_t)rank;
+    }
+    __syncwarp();
+    return __popc(m);
+}
+__device__ __forceinline__ void tok_drain_exact(const DevTags& tg, const uint8_t* __restrict__ bytes, int64_t total, uint32_t* __restrict__ rec,
+                                                int64_t r2, const TokWarpScratch& W, int first, int n, int lane) {
     if (lane < n) {
         const int64_t x = W.dpos[first + lane];
-        int is_close, cls, exotic;
-        const int len = tag_at<false>(tg, bytes, total, x, is_close, cls, exotic);
-        rec[rec_index(x >> 10, W.drank[first + lane], r2)] = pack_rec((int)(x & 1023), len, is_close, cls, exotic);
+        const PtrAcc A{bytes};
+        const int is_close = bytes[x + 1] == '/';
+        int cls = 0;
+        int64_t ex;
+        const int64_t tend = match_tag(tg, A, x, total, is_close != 0, cls, ex);
+        const int len = tend >= 0 ? (int)(tend - x) : 0;
+        rec[rec_index(x >> 10, W.drank[first + lane], r2)] = pack_rec((int)(x & 1023), len, is_close, len ? cls : 0, len && ex >= 0);
     }
 }
 
-// Warp-collective: lanes with `need` append (x, rank) to the warp's deferred list (counter in shared memory: the pairs of
-// ordinary text never come here and pay no register for it).  The list is drained between pairs (tokenize_kernel), so
-// it holds at most 31 + 2 * kRecPerStep entries.
+// Warp-collective: lanes with `need` append (x, rank) to the warp's list of fresh candidates (counter in shared memory:
+// the pairs without a '<' never come here and pay no register for it).  The list is drained between pairs
+// (tokenize_kernel), so it holds at most 31 + 2 * kRecPerStep entries.
 __device__ __forceinline__ bool tok_defer(TokWarpScratch& W, bool need, int64_t x, int rank, int lane) {
     const unsigned m = __ballot_sync(kFull, need);
     if (m) {
@@ -92,17 +122,14 @@ __device__ __forceinline__ bool tok_defer(TokWarpScratch& W, bool need, int64_t 
 // One 2 KiB pair of steps `pr` of the flat buffer, by one warp: lane j loads bytes [64j, 64j+64) with four 16-byte loads
 // (lanes 0-15 read the first step, lanes 16-31 the second), so one ballot and one divergent "look at the candidates"
 // branch serve two steps, and each lane has 64 bytes in flight.
-//   sparse pair (no lane has more than one '<', the usual case): every lane with a candidate matches it, ranks straight
-//     from the ballot;
-//   dense pair: the candidates are written, in position order, to a list in shared memory (ranks from a warp scan of the
-//     per-lane counts) and matched ONE PER LANE, so the expensive part (tag_at) runs once per 32 candidates instead of
-//     once per candidate of the busiest lane (adversarial text has 40 '<' per KiB in places: cfg5's tokenizer 1.16 ->
-//     0.65 ms); a candidate's record goes straight to its slot: its rank inside its step is its list index minus the
-//     step's first index.  Candidates whose window holds a fold-form lead byte need the exact byte-wise matcher: they are
-//     deferred to the warp's list (tok_defer) and matched 32 at a time between pairs (tok_drain): cfg5 0.69 -> 0.50 ms.
-//   The sparse path defers EVERY candidate (position and rank are known, the record slot waits): cfg3's tokenizer
-//     0.74 -> 0.69 ms (6.0 TB/s), cfg2 0.201 -> 0.192, cfg4 0.70 -> 0.68, cfg5 0.52 -> 0.48.  (Deferring only the
-//     candidates that need the exact matcher there cost more in ballots than it saved.)
+//   Every '<' found goes to the warp's list of fresh candidates with its position and its rank inside its step (the
+//   record slot it will fill) and is matched later, 32 at a time (tok_drain_fast / tok_drain_exact):
+//   sparse pair (no lane has more than one '<', the usual case): ranks straight from the ballot;
+//   dense pair: ranks from a warp scan of the per-lane counts, every lane writes its candidates in position order.
+//   History of this part: candidates matched where they are found by the lane that holds them; dense pairs compacted into
+//   a per-pair list and matched one per lane (cfg5 1.16 -> 0.65 ms); candidates that need the byte-wise matcher deferred
+//   across pairs (0.69 -> 0.50); every candidate of a sparse pair deferred (cfg3 0.74 -> 0.69 = 6.0 TB/s); every
+//   candidate of a dense pair too, and the byte-wise matcher as a second stage of the drain (cfg5 0.475 -> 0.396).
 // Returns true when something was deferred.
 // cnt / rec are indexed by absolute step (rec through rec_index); steps >= nsteps are not written, bytes at and beyond
 // `total` are never read.  A step with more than
@@ -159,42 +186,27 @@ __device__ __forceinline__ bool tokenize_pair(const DevTags& tg, const uint8_t* 
     }
     const int c0 = __shfl_sync(kFull, incl, 15), c1 = __shfl_sync(kFull, incl, 31) - c0;  // candidates of the two steps
     const bool bad0 = c0 > kRecPerStep, bad1 = c1 > kRecPerStep;
-    const int first1 = bad0 ? 0 : c0;                 // list index of the second step's first candidate
-    const int n_list = first1 + (bad1 ? 0 : c1);
-    {
-        const bool bad = half ? bad1 : bad0;
-        int idx = half ? first1 + (incl - nr - c0) : incl - nr;
-        if (!bad) {
-            unsigned long long m = (unsigned long long)lt0 | ((unsigned long long)lt1 << 32);
-            while (m) {
-                const int b = __ffsll((long long)m) - 1;
-                m &= m - 1;
-                W.list[idx++] = (uint16_t)(lane * 64 + b);
-            }
-        }
-    }
+    // every candidate straight to the warp's list of fresh candidates, in position order, with its rank inside its step
+    const bool ok0 = !bad0 && (pr << 1) < nsteps, ok1 = !bad1 && (pr << 1) + 1 < nsteps;
+    const int first1 = ok0 ? c0 : 0;
+    const int n_list = first1 + (ok1 ? c1 : 0);
+    const int nd0 = W.ndef;
     __syncwarp();
-    bool deferred = false;
-    for (int i0 = 0; i0 < n_list; i0 += 32) {
-        const int i = i0 + lane;
-        bool need = false;
-        int64_t x = 0;
-        int rank = 0;
-        if (i < n_list) {
-            const int pos = W.list[i];
-            const int sl = pos >> 10;
-            const int64_t st = (pr << 1) + sl;
-            if (st < nsteps) {
-                int is_close, cls, exotic;
-                x = (pr << 11) + pos;
-                const int len = tag_at<true>(tg, bytes, total, x, is_close, cls, exotic);
-                rank = i - (sl ? first1 : 0);
-                need = len < 0;
-                if (!need) rec[rec_index(st, rank, r2)] = pack_rec(pos & 1023, len, is_close, cls, exotic);
-            }
+    if (half ? ok1 : ok0) {
+        int rk = half ? incl - nr - c0 : incl - nr;  // rank of this lane's first candidate inside its step
+        int k = nd0 + (half ? first1 : 0) + rk;
+        unsigned long long m = (unsigned long long)lt0 | ((unsigned long long)lt1 << 32);
+        while (m) {
+            const int b = __ffsll((long long)m) - 1;
+            m &= m - 1;
+            W.dpos[k] = a + b;
+            W.drank[k] = (uint8_t)rk;
+            k++;
+            rk++;
         }
-        deferred |= tok_defer(W, need, x, rank, lane);
     }
+    if (lane == 0) W.ndef = nd0 + n_list;
+    const bool deferred = n_list > 0;
     if ((lane & 15) == 0 && step < nsteps) cnt[step] = (uint8_t)((half ? bad1 : bad0) ? kRecOverflow : (half ? c1 : c0));
     __syncwarp();
     return deferred;
@@ -219,7 +231,7 @@ __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant_
     const int64_t r2 = max_steps * kRecInline;  // where the second record array starts (words)
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
     TokWarpScratch& W = s_tok[threadIdx.x >> 5];
-    if (lane == 0) W.ndef = 0;
+    if (lane == 0) W.ndef = W.nex = 0;
     __syncwarp();
     for (int64_t pr = (begin >> 11) + (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); pr < npairs; pr += nwarps) {
         {   // this warp's next 2 KiB: get its sixteen lines into L2 now, one iteration of work ahead of their use
@@ -228,17 +240,33 @@ __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant_
         }
         if (!tokenize_pair(tg, bytes, total, nsteps, pr, lane, cnt, rec, r2, W)) continue;
         int nd = W.ndef;
-        if (nd >= 32) {  // full warps' worth of deferred candidates
+        if (nd >= 32) {  // full warps' worth of fresh candidates, and of candidates for the exact matcher
+            int nx = W.nex;
             do {
                 nd -= 32;
-                tok_drain(tg, bytes, total, rec, r2, W, nd, 32, lane);
+                nx += tok_drain_fast(tg, bytes, total, rec, r2, W, nd, 32, nx, lane);
+                if (nx >= 32) {
+                    nx -= 32;
+                    tok_drain_exact(tg, bytes, total, rec, r2, W, kTokDefer - nx - 32, 32, lane);
+                    __syncwarp();
+                }
             } while (nd >= 32);
-            __syncwarp();
-            if (lane == 0) W.ndef = nd;
+            if (lane == 0) {
+                W.ndef = nd;
+                W.nex = nx;
+            }
             __syncwarp();
         }
     }
-    if (W.ndef) tok_drain(tg, bytes, total, rec, r2, W, 0, W.ndef, lane);
+    {   // what is left at the end
+        int nx = W.nex;
+        const int nd = W.ndef;
+        if (nd) nx += tok_drain_fast(tg, bytes, total, rec, r2, W, 0, nd, nx, lane);
+        for (; nx > 0; nx -= 32) {
+            const int n = nx < 32 ? nx : 32;
+            tok_drain_exact(tg, bytes, total, rec, r2, W, kTokDefer - nx, n, lane);
+        }
+    }
 }
 
 }  // namespace qb

@@ -7,6 +7,12 @@
 
 namespace qb {
 
+// Programmatic dependent launch: a kernel launched with the stream-serialization attribute may be scheduled while the
+// kernel before it on the stream is still draining; everything it reads from that kernel comes after this wait (a no-op
+// for a kernel launched the ordinary way).
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+
 constexpr int kMaxTags = 16;
 constexpr int kNameStride = 24;
 constexpr int kHeldMax = 23;

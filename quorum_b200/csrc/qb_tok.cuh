@@ -219,6 +219,7 @@ __global__ void __launch_bounds__(256, 5) tokenize_kernel(const __grid_constant_
                                                        uint8_t* __restrict__ cnt, uint32_t* __restrict__ rec, int64_t max_steps,
                                                        unsigned long long* __restrict__ zero, int64_t zero_words) {
     __shared__ TokWarpScratch s_tok[8];
+    grid_dep_wait();
     // housekeeping for the kernel that follows on the stream: its look-back words and ticket start at zero
     if (blockIdx.x == 0)
         for (int64_t i = threadIdx.x; i < zero_words; i += blockDim.x) zero[i] = 0;

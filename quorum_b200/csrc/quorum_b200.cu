@@ -214,6 +214,7 @@ __global__ void __launch_bounds__(kThreads, 4)
 strip_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
                    int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first, TokSrc ts,
                    UnitDesc* __restrict__ desc, int lane_steps, RunPool pool, LongQueue lq) {
+    grid_dep_wait();
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     __shared__ int s_lc[kLaneCls][kThreads];  // lane walker: last closer per class, one column per thread
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -268,6 +269,7 @@ __global__ void __launch_bounds__(kThreads, 4)
 strip_count_long_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off,
                         int64_t n_resp, int64_t* __restrict__ klen, int64_t* __restrict__ first, TokSrc ts,
                         UnitDesc* __restrict__ desc, RunPool pool, LongQueue lq, int scanwalk) {
+    grid_dep_wait();
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     __shared__ int2 s_stage[kWarpsPerBlock][kDescRuns + 1];  // scan walker: the runs of a unit that fits a descriptor
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -416,6 +418,7 @@ __global__ void __launch_bounds__(256)
 request_offsets_kernel(const int64_t* __restrict__ in_off, const int64_t* __restrict__ req_off, int64_t n_req,
                        const int64_t* __restrict__ klen, int hide, int stream_join, int32_t sep_len, int64_t* __restrict__ dst,
                        int64_t* __restrict__ out_off, ReqScan scan) {
+    grid_dep_wait();
     __shared__ int64_t s_wsum[8];
     __shared__ int64_t s_excl, s_ticket;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -559,6 +562,7 @@ strip_copy_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restrict_
                   const int64_t* __restrict__ dst, int hide, const uint8_t* __restrict__ sep, int32_t sep_len,
                   uint8_t* __restrict__ out, int64_t* __restrict__ resp_out_len, const UnitDesc* __restrict__ desc,
                   TokSrc ts, RunPool pool) {
+    grid_dep_wait();
     __shared__ unsigned long long lastclose[kWarpsPerBlock][kMaxCls];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = in_off[n_resp];
@@ -647,6 +651,7 @@ stream_count_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restric
                     int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
                     int64_t* __restrict__ totals, TokSrc ts, StreamDesc* __restrict__ desc, int32_t* __restrict__ sid,
                     int lane_steps, CountScan scan) {
+    grid_dep_wait();
     __shared__ int64_t s_wsum[kWarpsPerBlock];
     __shared__ int64_t s_excl, s_ticket;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -756,6 +761,7 @@ __global__ void __launch_bounds__(256)
 stream_offsets_kernel(const int64_t* __restrict__ chunk_off, const int64_t* __restrict__ stream_off, int64_t n_streams,
                       const int64_t* __restrict__ bases, int64_t* __restrict__ out_chunk_off, const StreamDesc* __restrict__ desc,
                       const int32_t* __restrict__ sid) {
+    grid_dep_wait();
     // PER boundaries per thread; a warp takes 32 * PER consecutive ones, lane-interleaved (coalesced)
     const int64_t cb = stream_off[0], nb = stream_off[n_streams] - cb;  // boundary cb + 1 + i ends chunk cb + i, i < nb
     if (blockIdx.x == 0 && threadIdx.x == 0) out_chunk_off[cb] = bases[0];
@@ -846,6 +852,7 @@ stream_finish_kernel(const __grid_constant__ DevTags tg, const uint8_t* __restri
                      int64_t n_streams, const StreamState* st_in, StreamState* st_out, uint32_t flags,
                      const int64_t* __restrict__ bases, uint8_t* __restrict__ out, int64_t* __restrict__ out_chunk_off,
                      const StreamDesc* __restrict__ desc) {
+    grid_dep_wait();
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t total = chunk_off[n_chunks];
     for (int64_t s = (int64_t)blockIdx.x * kWarpsPerBlock + wib; s < n_streams; s += (int64_t)gridDim.x * kWarpsPerBlock) {
@@ -894,6 +901,28 @@ __global__ void widen_i32_kernel(const int32_t* __restrict__ v, int64_t n, int64
 __global__ void lengths_i32_kernel(const int64_t* __restrict__ off, int64_t n, int32_t* __restrict__ len) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         len[i] = (int32_t)(off[i + 1] - off[i]);
+}
+
+// Launch with programmatic stream serialization (see grid_dep_wait): the next kernel's blocks are scheduled while the
+// previous kernel's last blocks finish, which takes the ~2 us launch gap between the four or five kernels of a call
+// off the critical path.  QB200_PDL=0 launches the ordinary way.
+static bool pdl_on() {
+    static const bool on = !(getenv("QB200_PDL") && atoi(getenv("QB200_PDL")) == 0);
+    return on;
+}
+template <class... KArgs, class... Args>
+static void launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t stream, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_on() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -1047,7 +1076,7 @@ static TokSrc launch_tokenizer(const DevTags& tg, const uint8_t* bytes, const in
     const int64_t cap = 148 * 32;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    tokenize_kernel<<<(unsigned)blocks, 256, 0, stream>>>(tg, bytes, off, idx, n, cnt, rec, st, zero, zero_words);
+    launch_pdl(tokenize_kernel, (unsigned)((unsigned)blocks), 256, stream, tg, bytes, off, idx, n, cnt, rec, st, zero, zero_words);
     LAUNCHED("tokenize_kernel");
     ts.cnt = cnt;
     ts.rec = rec;
@@ -1157,11 +1186,11 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
         CUDA_TRY(cudaMemsetAsync(scan_words, 0, (size_t)(nblk_req + 4) * 8, stream));
     }
     if (hide && n_resp > 0) {
-        strip_count_kernel<<<grid_for((n_resp + 31) / 32), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts,
+        launch_pdl(strip_count_kernel, (unsigned)(grid_for((n_resp + 31) / 32)), kThreads, stream, tags->dev, in_bytes, in_off, n_resp, klen, first, ts,
                                                                                  ts.cnt ? desc : nullptr, lane_steps, pool, lq);
         LAUNCHED("strip_count_kernel");
         if (ts.cnt) {
-            strip_count_long_kernel<<<4 * sm_count(), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, ts, desc, pool,
+            launch_pdl(strip_count_long_kernel, (unsigned)(4 * sm_count()), kThreads, stream, tags->dev, in_bytes, in_off, n_resp, klen, first, ts, desc, pool,
                                                                             lq, env_int("QB200_SCANWALK", 1));
             LAUNCHED("strip_count_long_kernel");
         }
@@ -1172,11 +1201,11 @@ int qb200_strip_concat_batch(const qb200_tags* tags, const uint8_t* in_bytes, co
         rs.ticket = (unsigned int*)(scan_words + nblk_req + 1);
         rs.chain = chain ? 1 : 0;
         int64_t g = nblk_req < 148 * 8 ? nblk_req : 148 * 8;
-        request_offsets_kernel<<<(unsigned)(g < 1 ? 1 : g), 256, 0, stream>>>(in_off, req_off, n_req, klen, hide, sj, sep_len, dst, out_off, rs);
+        launch_pdl(request_offsets_kernel, (unsigned)((unsigned)(g < 1 ? 1 : g)), 256, stream, in_off, req_off, n_req, klen, hide, sj, sep_len, dst, out_off, rs);
         LAUNCHED("request_offsets_kernel");
     }
     if (n_resp > 0) {
-        strip_copy_kernel<<<grid_for(n_resp), kThreads, 0, stream>>>(tags->dev, in_bytes, in_off, n_resp, klen, first, dst,
+        launch_pdl(strip_copy_kernel, (unsigned)(grid_for(n_resp)), kThreads, stream, tags->dev, in_bytes, in_off, n_resp, klen, first, dst,
                                                                     hide, sep, sep_len, out_bytes, resp_out_len,
                                                                     (hide && ts.cnt) ? desc : nullptr, ts, pool);
         LAUNCHED("strip_copy_kernel");
@@ -1255,7 +1284,7 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
     // chained call: this call's output starts where out_chunk_off[first chunk of the call] says (written by the call before)
     if (use_tokens) {  // prefix sum inside the count kernel (look-back words live where the totals would)
         CountScan cs{bases, scan_state, scan_ticket, chain ? out_chunk_off : nullptr, chain ? stream_off : nullptr};
-        stream_count_kernel<true><<<grid_for((n_streams + 31) / 32), kThreads, 0, stream>>>(
+        launch_pdl(stream_count_kernel<true>, (unsigned)(grid_for((n_streams + 31) / 32)), kThreads, stream, 
             tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, si, so, flags, totals, ts, desc, sid, lane_steps, cs);
         LAUNCHED("stream_count_kernel");
     } else {
@@ -1271,10 +1300,10 @@ static int stream_feed_general(const qb200_tags* tags, const uint8_t* chunk_byte
         int64_t nb = (n_chunks + 256 * kOffsetsPer - 1) / (256 * kOffsetsPer);
         if (nb > 148 * 64) nb = 148 * 64;
         if (nb < 1) nb = 1;
-        stream_offsets_kernel<kOffsetsPer><<<(unsigned)nb, 256, 0, stream>>>(chunk_off, stream_off, n_streams, bases, out_chunk_off, desc,
+        launch_pdl(stream_offsets_kernel<kOffsetsPer>, (unsigned)((unsigned)nb), 256, stream, chunk_off, stream_off, n_streams, bases, out_chunk_off, desc,
                                                                             sid);
         LAUNCHED("stream_offsets_kernel");
-        stream_finish_kernel<<<grid_for(n_streams), kThreads, 0, stream>>>(
+        launch_pdl(stream_finish_kernel, (unsigned)(grid_for(n_streams)), kThreads, stream, 
             tags->dev, chunk_bytes, chunk_off, n_chunks, stream_off, n_streams, si, so, flags, bases, out_bytes, out_chunk_off, desc);
         LAUNCHED("stream_finish_kernel");
     } else {

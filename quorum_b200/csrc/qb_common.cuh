@@ -9,7 +9,8 @@ namespace qb {
 
 // Programmatic dependent launch: a kernel launched with the stream-serialization attribute may be scheduled while the
 // kernel before it on the stream is still draining; everything it reads from that kernel comes after this wait (a no-op
-// for a kernel launched the ordinary way).
+// for a kernel launched the ordinary way).  (An explicit griddepcontrol.launch_dependents right behind the wait, so that
+// the next kernel's blocks take their slots while this one's last blocks run: cfg2 0.478 -> 0.485 ms, cfg3 1.889 -> 1.886.)
 __device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 
